@@ -1,0 +1,34 @@
+# Builds librtb200.so (the product: host scene API + sm_100a kernels behind the C ABI) and the
+# CPU oracle (test infrastructure).  `python -c "import __graft_entry__ as g; g.build()"` runs this.
+NVCC ?= nvcc
+CSRC := raytracing_rust_b200/csrc
+LIB := raytracing_rust_b200/librtb200.so
+GENCODE := -gencode arch=compute_100a,code=sm_100a
+NVCCFLAGS := -O3 -std=c++17 $(GENCODE) -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unknown-pragmas -Iinclude -I$(CSRC) \
+             -Xptxas -v --expt-relaxed-constexpr
+HOST_SRCS := $(CSRC)/scene.cpp $(CSRC)/scenes_named.cpp $(CSRC)/flatten.cpp
+CU_SRCS := $(CSRC)/render.cu $(CSRC)/wavefront.cu
+HDRS := $(wildcard include/*.h include/*.hpp $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh)
+OBJS := $(patsubst $(CSRC)/%.cpp,build/%.o,$(HOST_SRCS)) $(patsubst $(CSRC)/%.cu,build/%.cu.o,$(CU_SRCS))
+
+all: $(LIB) oracle
+
+build/%.o: $(CSRC)/%.cpp $(HDRS)
+	@mkdir -p build
+	g++ -O2 -std=c++17 -fPIC -Wall -Wextra -Iinclude -I$(CSRC) -c $< -o $@
+
+build/%.cu.o: $(CSRC)/%.cu $(HDRS)
+	@mkdir -p build
+	$(NVCC) $(NVCCFLAGS) -c $< -o $@ 2> build/$*.ptxas.log || (cat build/$*.ptxas.log; false)
+
+$(LIB): $(OBJS)
+	$(NVCC) -shared $(GENCODE) -o $@ $(OBJS) -cudart static
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -rf build $(LIB)
+	$(MAKE) -C oracle clean
+
+.PHONY: all oracle clean

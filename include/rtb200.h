@@ -1,0 +1,181 @@
+/* rtb200.h — C ABI of librtb200.so, the B200 (sm_100a) path tracer that replaces the
+ * per-pixel Monte-Carlo hot path of DrStiev/raytracing_rust:
+ *     create_image (tests/test.rs:55-85)  ->  color (src/color.rs:6-23)
+ *     -> Hittable::hit / Material::scatter,emitted / Texture::value.
+ *
+ * The reference has no FFI; its seam is the trait trio plus the `::new` constructors.
+ * Each entry point below names the reference item it stands in for.  A Rust `-sys` crate
+ *  binds exactly these symbols.
+ *
+ * Conventions: every call returns 0 on success, non-zero on error (rtb_last_error() has the
+ * text); builder calls return a handle >= 0 or a negative error.  A scene and its handles are
+ * owned by one rtb_scene and freed together.  Not thread-safe per scene.  Render calls block
+ * until the image is in the caller's host buffers.  There is NO CPU fallback: render and
+ * closest-hit calls fail with RTB_ERR_NO_DEVICE when no CUDA device is usable.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "rtb_scene_format.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rtb_scene rtb_scene;
+
+enum RtbStatus {
+  RTB_OK = 0,
+  RTB_ERR_INVALID = -1,   /* bad handle / argument */
+  RTB_ERR_NO_DEVICE = -2, /* no CUDA device / driver */
+  RTB_ERR_CUDA = -3,      /* a CUDA call failed */
+  RTB_ERR_NO_BBOX = -4,   /* reference: panic!("No bounding box in BVHNode") src/bvh.rs:30,58 */
+  RTB_ERR_IO = -5
+};
+
+enum RtbBackground {
+  RTB_BG_BLACK = 0, /* src/color.rs:21 — the reference as written */
+  RTB_BG_SKY = 1    /* the gradient commented out at src/color.rs:18-20 (lit variant) */
+};
+
+enum RtbPipeline {
+  RTB_PIPE_AUTO = 0,
+  RTB_PIPE_MEGAKERNEL = 1, /* one persistent kernel, path regeneration */
+  RTB_PIPE_WAVEFRONT = 2   /* raygen / extend / per-material shade queues */
+};
+
+const char* rtb_last_error(void);
+const char* rtb_version(void);
+/* number of usable CUDA devices (0 when there is none; never fails) */
+int rtb_device_count(void);
+
+/* ---- scene lifetime ------------------------------------------------------------------- */
+rtb_scene* rtb_scene_create(void);
+void rtb_scene_destroy(rtb_scene*);
+
+/* ---- textures: src/texture.rs --------------------------------------------------------- */
+int rtb_tex_solid(rtb_scene*, double r, double g, double b);              /* SolidTexture::new :14 */
+int rtb_tex_checker(rtb_scene*, int odd, int even);                       /* CheckerTexture::new :34 */
+/* NoiseTexture::new :57.  The reference draws fresh Perlin tables from thread_rng
+ * (src/perlin.rs:12-36); here the tables come from `seed` (same construction, reproducible).
+ * Cloning a NoiseTexture shares its tables: pass the same handle twice. */
+int rtb_tex_noise(rtb_scene*, double scale, uint64_t seed);
+/* same, with caller-provided tables (ranvec[256*3], perm_{x,y,z}[256]) */
+int rtb_tex_noise_tables(rtb_scene*, double scale, const double* ranvec, const uint8_t* perm_x,
+                         const uint8_t* perm_y, const uint8_t* perm_z);
+int rtb_tex_image(rtb_scene*, const uint8_t* rgb8, uint32_t nx, uint32_t ny); /* ImageTexture::new :81 */
+
+/* ---- materials: src/material.rs ------------------------------------------------------- */
+int rtb_mat_lambertian(rtb_scene*, int albedo_tex);          /* Lambertian::new :41 */
+int rtb_mat_metal(rtb_scene*, int albedo_tex, double fuzz);  /* Metal::new :67 */
+int rtb_mat_dielectric(rtb_scene*, double ref_idx);          /* Dielectric::new :100 */
+int rtb_mat_diffuse_light(rtb_scene*, int emit_tex);         /* DiffuseLight::new :138 */
+int rtb_mat_isotropic(rtb_scene*, int albedo_tex);           /* Isotropic::new :159 */
+
+/* ---- hittables ------------------------------------------------------------------------ */
+int rtb_obj_sphere(rtb_scene*, const double center[3], double radius, int mat); /* src/sphere.rs:27 */
+int rtb_obj_moving_sphere(rtb_scene*, const double c0[3], const double c1[3], double t0, double t1,
+                          double radius, int mat);                              /* src/sphere.rs:97 */
+int rtb_obj_rect(rtb_scene*, int plane /*RtbPlane*/, double x0, double y0, double x1, double y1,
+                 double k, int mat);                                            /* src/rect.rs:25 */
+int rtb_obj_cube(rtb_scene*, const double p_min[3], const double p_max[3], int mat); /* src/cube.rs:15 */
+int rtb_obj_flip_normals(rtb_scene*, int obj);                                  /* src/hittable.rs:72 */
+int rtb_obj_rotate(rtb_scene*, int axis /*RtbAxis*/, int obj, double angle_deg); /* src/rotate.rs:30 */
+int rtb_obj_translate(rtb_scene*, int obj, const double offset[3]);             /* src/traslate.rs:12 */
+int rtb_obj_constant_medium(rtb_scene*, int boundary, double density, int tex); /* src/medium.rs:18 */
+int rtb_obj_list(rtb_scene*, const int* objs, int n);         /* HittableList push order, src/hittable.rs:23-34 */
+/* BVHNode::new(&mut [Rc<dyn Hittable>], time0, time1), src/bvh.rs:17.  Fails with
+ * RTB_ERR_NO_BBOX if n == 0.  `seed` drives the oracle's split-axis stream; the GPU builds its
+ * own SAH tree over the same primitives (closest-hit results do not depend on the tree). */
+int rtb_obj_bvh(rtb_scene*, const int* objs, int n, double time0, double time1, uint64_t seed);
+
+/* ---- named scenes: tests/test.rs:89-523 ---------------------------------------------------
+ * name in {"random_scene","two_spheres","two_perlin_sphere","earth","simple_light",
+ *          "cornell_box","cornell_smoke","final_scene"} as written in the reference, plus the
+ * labelled lit variants {"final_scene_lit","cornell_smoke_book"}.  `seed` replaces thread_rng
+ * in the constructors; `earth_rgb8` (1024x512 decoded earthmap.jpg) is needed by earth and
+ * final_scene*, else may be NULL.  Returns the world handle; *camera gets the camera the
+ * matching #[test] uses (tests/test.rs:543-830) for the given nx, ny. */
+int rtb_scene_named(rtb_scene*, const char* name, uint64_t seed, const uint8_t* earth_rgb8,
+                    uint32_t earth_nx, uint32_t earth_ny, int nx, int ny, RtbCamera* camera);
+
+/* ---- serialisation (.rtscene, include/rtb_scene_format.h) ----------------------------- */
+size_t rtb_scene_serialized_size(const rtb_scene*);
+int rtb_scene_serialize(const rtb_scene*, void* buf, size_t cap);
+rtb_scene* rtb_scene_deserialize(const void* buf, size_t len);
+/* number of leaf-primitive IDs under `world` (depth-first insertion order; a Cube owns 6,
+ * in the order of src/cube.rs:21-74) */
+int rtb_scene_prim_count(rtb_scene*, int world);
+
+/* ---- rendering ---------------------------------------------------------------------------- */
+typedef struct rtb_render_opts {
+  int max_depth;       /* 50  (src/color.rs:9) */
+  double t_min;        /* 1e-3 (src/color.rs:7) */
+  int background;      /* RtbBackground */
+  uint64_t seed;       /* render seed: Philox4x32-10 key; counter = (block, pixel, sample) */
+  int sample_begin;    /* this call renders samples s = sample_begin + i*sample_stride < ns */
+  int sample_stride;   /* (rank, world_size) for sample sharding across GPUs; 0,1 for all */
+  int pipeline;        /* RtbPipeline */
+  int device;          /* CUDA device ordinal */
+  int collect_stats;   /* count segments / node tests / primitive tests (slower, untimed runs) */
+  int reserved[7];
+} rtb_render_opts;
+
+typedef struct rtb_stats {
+  uint64_t paths, segments;
+  uint64_t node_tests, prim_tests, medium_tests;
+  uint64_t shade[5];        /* per RtbMatType */
+  uint64_t tex_evals[4];    /* per RtbTexType */
+  uint64_t kernel_launches; /* launches of this library's kernels in the call */
+  double device_ms;         /* CUDA-event time of the render kernels */
+  uint64_t reserved[8];
+} rtb_stats;
+
+void rtb_render_opts_default(rtb_render_opts*);
+
+/* create_image(ny, nx, ns, cam, world) -> String, tests/test.rs:55-85 (argument order is the
+ * caller's business here: nx is the width).  Host buffers; either output may be NULL.
+ *   out_sum_rgb : 3*nx*ny floats, row 0 = top of the image (j = ny-1), SUM of the radiance
+ *                 samples this call rendered (divide by the sample count for the mean)
+ *   out_rgb8    : 3*nx*ny bytes, the reference quantisation tests/test.rs:71-78 of the mean
+ *                 (only meaningful when the call renders all ns samples) */
+int rtb_render(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns,
+               const rtb_render_opts*, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
+
+/* Device-resident variant for multi-GPU and benchmarking: the scene is uploaded once
+ * (rtb_scene_upload), samples are ADDED into d_sum_rgb (device pointer, 3*nx*ny floats,
+ * caller-zeroed) on `cuda_stream` (a cudaStream_t cast to void*, NULL = default stream)
+ * without synchronising. */
+int rtb_scene_upload(rtb_scene*, int world, int device);
+int rtb_render_device(rtb_scene*, const RtbCamera*, int nx, int ny, int ns, const rtb_render_opts*,
+                      float* d_sum_rgb, void* cuda_stream, rtb_stats*);
+/* tests/test.rs:71-78: /ns, sqrt, clamp[0,1], (255.99*c) as i32 — on device */
+int rtb_resolve_device(const float* d_sum_rgb, int nx, int ny, int ns, uint8_t* d_rgb8,
+                       void* cuda_stream);
+
+/* Closest-hit query for the primitive-ID parity test: Hittable::hit(ray, t_min, f64::MAX)
+ * (src/color.rs:7) with ConstantMedium objects skipped.  rays = n x {ox,oy,oz,dx,dy,dz,time}
+ * (host, double); out_prim[i] = primitive ID or -1; out_t[i] = t (undefined on a miss). */
+int rtb_closest_hit(rtb_scene*, int world, const double* rays, size_t n, double t_min, int device,
+                    int32_t* out_prim, float* out_t);
+/* Camera::get_ray (src/camera.rs:53-67) for the fixed parity batch: ray i is sample `s` of
+ * pixel i of the nx*ny image, drawn from the same Philox stream the renderer uses; host
+ * output n x 7 doubles.  Pure host code (no device). */
+int rtb_primary_rays(const RtbCamera*, int nx, int ny, int s, uint64_t seed, double* out_rays);
+
+/* Texture::value (src/texture.rs:4-6) over a batch, evaluated by the device texture code —
+ * a test hook for Perlin / checker / image parity.  uvp = n x {u,v,px,py,pz} (host, double);
+ * out = n x {r,g,b} (host, float). */
+int rtb_debug_texture_value(rtb_scene*, int world, int tex, const double* uvp, size_t n, int device,
+                            float* out);
+
+/* P3 text exactly as tests/test.rs:59,79: "P3\n{nx} {ny}\n255\n" + "{r} {g} {b}\n" per pixel.
+ * Returns the byte count (excluding NUL); writes at most cap bytes. */
+size_t rtb_ppm_p3(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

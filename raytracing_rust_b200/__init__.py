@@ -1,0 +1,341 @@
+"""raytracing_rust_b200 — Python host mirror of the rtb200 C ABI (include/rtb200.h).
+
+The product is ``librtb200.so`` (C++ scene host + hand-written sm_100a kernels).  This module is a
+thin ctypes binding used by the tests and ``bench.py``; it mirrors the reference crate's
+constructor names (``Sphere::new`` -> :meth:`Scene.sphere`, ... ; raytracing_rust
+``src/*.rs``) and its driver ``create_image`` (``tests/test.rs:55-85``).
+
+There is no CPU fallback: importing without the built library raises, and every render call
+fails loudly when no CUDA device is usable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+_LIB_PATH = _HERE / "librtb200.so"
+ASSETS = _HERE.parent / "assets"
+
+if not _LIB_PATH.exists():
+    raise ImportError(
+        f"{_LIB_PATH} is missing: build it with `make` (or `python -c 'import __graft_entry__ as g; g.build()'`). "
+        "rtb200 has no CPU fallback."
+    )
+lib = C.CDLL(str(_LIB_PATH))
+
+PLANE_YZ, PLANE_ZX, PLANE_XY = 0, 1, 2
+AXIS_X, AXIS_Y, AXIS_Z = 0, 1, 2
+BG_BLACK, BG_SKY = 0, 1
+PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT = 0, 1, 2
+
+NAMED_SCENES = (
+    "random_scene", "two_spheres", "two_perlin_sphere", "earth", "simple_light",
+    "cornell_box", "cornell_smoke", "final_scene",
+)
+LIT_VARIANTS = ("final_scene_lit", "cornell_smoke_book")
+
+
+class RtbCamera(C.Structure):
+    _fields_ = [
+        ("look_from", C.c_double * 3), ("look_at", C.c_double * 3), ("view_up", C.c_double * 3),
+        ("vertical_fov", C.c_double), ("aspect", C.c_double), ("aperture", C.c_double),
+        ("focus_dist", C.c_double), ("time0", C.c_double), ("time1", C.c_double),
+    ]
+
+
+class RenderOpts(C.Structure):
+    _fields_ = [
+        ("max_depth", C.c_int), ("t_min", C.c_double), ("background", C.c_int), ("seed", C.c_uint64),
+        ("sample_begin", C.c_int), ("sample_stride", C.c_int), ("pipeline", C.c_int), ("device", C.c_int),
+        ("collect_stats", C.c_int), ("reserved", C.c_int * 7),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("paths", C.c_uint64), ("segments", C.c_uint64), ("node_tests", C.c_uint64),
+        ("prim_tests", C.c_uint64), ("medium_tests", C.c_uint64), ("shade", C.c_uint64 * 5),
+        ("tex_evals", C.c_uint64 * 4), ("kernel_launches", C.c_uint64), ("device_ms", C.c_double),
+        ("reserved", C.c_uint64 * 8),
+    ]
+
+    def as_dict(self):
+        return {
+            "paths": self.paths, "segments": self.segments, "node_tests": self.node_tests,
+            "prim_tests": self.prim_tests, "medium_tests": self.medium_tests, "shade": list(self.shade),
+            "tex_evals": list(self.tex_evals), "kernel_launches": self.kernel_launches,
+            "device_ms": self.device_ms,
+        }
+
+
+def _sig(name, restype, *argtypes):
+    f = getattr(lib, name)
+    f.restype = restype
+    f.argtypes = list(argtypes)
+    return f
+
+
+_vp, _i, _d, _u64, _sz = C.c_void_p, C.c_int, C.c_double, C.c_uint64, C.c_size_t
+_dp, _u8p = C.POINTER(C.c_double), C.POINTER(C.c_uint8)
+
+_sig("rtb_last_error", C.c_char_p)
+_sig("rtb_version", C.c_char_p)
+_sig("rtb_device_count", _i)
+_sig("rtb_scene_create", _vp)
+_sig("rtb_scene_destroy", None, _vp)
+_sig("rtb_tex_solid", _i, _vp, _d, _d, _d)
+_sig("rtb_tex_checker", _i, _vp, _i, _i)
+_sig("rtb_tex_noise", _i, _vp, _d, _u64)
+_sig("rtb_tex_noise_tables", _i, _vp, _d, _vp, _vp, _vp, _vp)
+_sig("rtb_tex_image", _i, _vp, _vp, C.c_uint32, C.c_uint32)
+_sig("rtb_mat_lambertian", _i, _vp, _i)
+_sig("rtb_mat_metal", _i, _vp, _i, _d)
+_sig("rtb_mat_dielectric", _i, _vp, _d)
+_sig("rtb_mat_diffuse_light", _i, _vp, _i)
+_sig("rtb_mat_isotropic", _i, _vp, _i)
+_sig("rtb_obj_sphere", _i, _vp, _dp, _d, _i)
+_sig("rtb_obj_moving_sphere", _i, _vp, _dp, _dp, _d, _d, _d, _i)
+_sig("rtb_obj_rect", _i, _vp, _i, _d, _d, _d, _d, _d, _i)
+_sig("rtb_obj_cube", _i, _vp, _dp, _dp, _i)
+_sig("rtb_obj_flip_normals", _i, _vp, _i)
+_sig("rtb_obj_rotate", _i, _vp, _i, _i, _d)
+_sig("rtb_obj_translate", _i, _vp, _i, _dp)
+_sig("rtb_obj_constant_medium", _i, _vp, _i, _d, _i)
+_sig("rtb_obj_list", _i, _vp, C.POINTER(C.c_int), _i)
+_sig("rtb_obj_bvh", _i, _vp, C.POINTER(C.c_int), _i, _d, _d, _u64)
+_sig("rtb_scene_named", _i, _vp, C.c_char_p, _u64, _vp, C.c_uint32, C.c_uint32, _i, _i, C.POINTER(RtbCamera))
+_sig("rtb_scene_serialized_size", _sz, _vp)
+_sig("rtb_scene_serialize", _i, _vp, _vp, _sz)
+_sig("rtb_scene_deserialize", _vp, _vp, _sz)
+_sig("rtb_scene_prim_count", _i, _vp, _i)
+_sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
+_sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
+_sig("rtb_scene_upload", _i, _vp, _i, _i)
+_sig("rtb_render_device", _i, _vp, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
+_sig("rtb_resolve_device", _i, _vp, _i, _i, _i, _vp, _vp)
+_sig("rtb_closest_hit", _i, _vp, _i, _vp, _sz, _d, _i, _vp, _vp)
+_sig("rtb_debug_texture_value", _i, _vp, _i, _i, _vp, _sz, _i, _vp)
+_sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
+_sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
+
+
+class RtbError(RuntimeError):
+    def __init__(self, code, where):
+        self.code = code
+        super().__init__(f"{where}: [{code}] {lib.rtb_last_error().decode()}")
+
+
+def _h(code, where):
+    if code < 0:
+        raise RtbError(code, where)
+    return code
+
+
+def _vec3(v):
+    return (C.c_double * 3)(*[float(x) for x in v])
+
+
+def device_count() -> int:
+    return lib.rtb_device_count()
+
+
+def earth_rgb8() -> np.ndarray:
+    """Decoded texture/earthmap.jpg (1024x512 RGB8), staged in assets/ (SURVEY F9)."""
+    a = np.fromfile(ASSETS / "earthmap_1024x512.rgb8", dtype=np.uint8)
+    return a.reshape(512, 1024, 3)
+
+
+def default_opts(**kw) -> RenderOpts:
+    o = RenderOpts()
+    lib.rtb_render_opts_default(C.byref(o))
+    for k, v in kw.items():
+        setattr(o, k, v)
+    return o
+
+
+def camera(look_from, look_at, view_up, vertical_fov, aspect, aperture, focus_dist, time0, time1) -> RtbCamera:
+    """Camera::new, src/camera.rs:21-31 (same argument order)."""
+    c = RtbCamera()
+    c.look_from[:] = look_from
+    c.look_at[:] = look_at
+    c.view_up[:] = view_up
+    c.vertical_fov, c.aspect, c.aperture = vertical_fov, aspect, aperture
+    c.focus_dist, c.time0, c.time1 = focus_dist, time0, time1
+    return c
+
+
+class Scene:
+    """One rtb_scene.  Builder methods return handles and mirror the crate's constructors."""
+
+    def __init__(self, _ptr=None):
+        self._p = _ptr if _ptr is not None else lib.rtb_scene_create()
+        if not self._p:
+            raise RtbError(-1, "scene_create")
+        self._keep = []
+
+    def __del__(self):
+        p, self._p = getattr(self, "_p", None), None
+        if p:
+            lib.rtb_scene_destroy(p)
+
+    # -- textures (src/texture.rs)
+    def solid(self, r, g, b):
+        return _h(lib.rtb_tex_solid(self._p, r, g, b), "tex_solid")
+
+    def checker(self, odd, even):
+        return _h(lib.rtb_tex_checker(self._p, odd, even), "tex_checker")
+
+    def noise(self, scale, seed=0x5EED):
+        return _h(lib.rtb_tex_noise(self._p, scale, seed), "tex_noise")
+
+    def image(self, rgb8: np.ndarray):
+        a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+        ny, nx = a.shape[0], a.shape[1]
+        return _h(lib.rtb_tex_image(self._p, a.ctypes.data, nx, ny), "tex_image")
+
+    # -- materials (src/material.rs)
+    def lambertian(self, tex):
+        return _h(lib.rtb_mat_lambertian(self._p, tex), "mat_lambertian")
+
+    def metal(self, tex, fuzz):
+        return _h(lib.rtb_mat_metal(self._p, tex, fuzz), "mat_metal")
+
+    def dielectric(self, ref_idx):
+        return _h(lib.rtb_mat_dielectric(self._p, ref_idx), "mat_dielectric")
+
+    def diffuse_light(self, tex):
+        return _h(lib.rtb_mat_diffuse_light(self._p, tex), "mat_diffuse_light")
+
+    def isotropic(self, tex):
+        return _h(lib.rtb_mat_isotropic(self._p, tex), "mat_isotropic")
+
+    # -- hittables
+    def sphere(self, center, radius, mat):
+        return _h(lib.rtb_obj_sphere(self._p, _vec3(center), radius, mat), "obj_sphere")
+
+    def moving_sphere(self, c0, c1, t0, t1, radius, mat):
+        return _h(lib.rtb_obj_moving_sphere(self._p, _vec3(c0), _vec3(c1), t0, t1, radius, mat), "obj_moving_sphere")
+
+    def rect(self, plane, x0, y0, x1, y1, k, mat):
+        return _h(lib.rtb_obj_rect(self._p, plane, x0, y0, x1, y1, k, mat), "obj_rect")
+
+    def cube(self, p_min, p_max, mat):
+        return _h(lib.rtb_obj_cube(self._p, _vec3(p_min), _vec3(p_max), mat), "obj_cube")
+
+    def flip_normals(self, obj):
+        return _h(lib.rtb_obj_flip_normals(self._p, obj), "obj_flip_normals")
+
+    def rotate(self, axis, obj, angle_deg):
+        return _h(lib.rtb_obj_rotate(self._p, axis, obj, angle_deg), "obj_rotate")
+
+    def translate(self, obj, offset):
+        return _h(lib.rtb_obj_translate(self._p, obj, _vec3(offset)), "obj_translate")
+
+    def constant_medium(self, boundary, density, tex):
+        return _h(lib.rtb_obj_constant_medium(self._p, boundary, density, tex), "obj_constant_medium")
+
+    def list(self, objs):
+        arr = (C.c_int * len(objs))(*objs)
+        return _h(lib.rtb_obj_list(self._p, arr, len(objs)), "obj_list")
+
+    def bvh(self, objs, t0=0.0, t1=1.0, seed=0):
+        arr = (C.c_int * len(objs))(*objs)
+        return _h(lib.rtb_obj_bvh(self._p, arr, len(objs), t0, t1, seed), "obj_bvh")
+
+    # -- named scenes (tests/test.rs:89-523)
+    @classmethod
+    def named(cls, name, nx, ny, seed=0x5EED):
+        """Returns (scene, world_handle, camera) for one of NAMED_SCENES / LIT_VARIANTS."""
+        s = cls()
+        cam = RtbCamera()
+        e = earth_rgb8() if name in ("earth", "final_scene", "final_scene_lit") else None
+        ep = e.ctypes.data if e is not None else None
+        w = _h(lib.rtb_scene_named(s._p, name.encode(), seed, ep, 1024 if e is not None else 0,
+                                   512 if e is not None else 0, nx, ny, C.byref(cam)), f"scene_named({name})")
+        return s, w, cam
+
+    # -- serialisation
+    def serialize(self) -> bytes:
+        n = lib.rtb_scene_serialized_size(self._p)
+        buf = C.create_string_buffer(n)
+        _h(lib.rtb_scene_serialize(self._p, buf, n), "scene_serialize")
+        return buf.raw
+
+    @classmethod
+    def deserialize(cls, data: bytes):
+        p = lib.rtb_scene_deserialize(data, len(data))
+        if not p:
+            raise RtbError(-1, "scene_deserialize")
+        return cls(_ptr=p)
+
+    def prim_count(self, world):
+        return _h(lib.rtb_scene_prim_count(self._p, world), "scene_prim_count")
+
+    # -- rendering
+    def render(self, world, cam, nx, ny, ns, opts=None, want_sum=True, want_rgb8=True, want_stats=False):
+        """create_image (tests/test.rs:55-85) with host buffers.  Returns (sum_rgb float32
+        [ny,nx,3] or None, rgb8 uint8 [ny,nx,3] or None, stats dict or None)."""
+        o = opts if opts is not None else default_opts()
+        out_sum = np.empty((ny, nx, 3), np.float32) if want_sum else None
+        out_rgb8 = np.empty((ny, nx, 3), np.uint8) if want_rgb8 else None
+        st = Stats() if want_stats else None
+        _h(lib.rtb_render(self._p, world, C.byref(cam), nx, ny, ns, C.byref(o),
+                          out_sum.ctypes.data if want_sum else None, out_rgb8.ctypes.data if want_rgb8 else None,
+                          C.byref(st) if want_stats else None), "render")
+        return out_sum, out_rgb8, (st.as_dict() if want_stats else None)
+
+    def upload(self, world, device=0):
+        _h(lib.rtb_scene_upload(self._p, world, device), "scene_upload")
+
+    def render_device(self, cam, nx, ny, ns, opts, d_sum_ptr: int, stream: int = 0, want_stats=False):
+        st = Stats() if want_stats else None
+        _h(lib.rtb_render_device(self._p, C.byref(cam), nx, ny, ns, C.byref(opts), d_sum_ptr, stream,
+                                 C.byref(st) if want_stats else None), "render_device")
+        return st.as_dict() if want_stats else None
+
+    def closest_hit(self, world, rays: np.ndarray, t_min=1e-3, device=0):
+        """rays: [n,7] float64 {o, d, time}.  Returns (prim int32 [n], t float32 [n])."""
+        r = np.ascontiguousarray(rays, dtype=np.float64)
+        n = r.shape[0]
+        prim = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        _h(lib.rtb_closest_hit(self._p, world, r.ctypes.data, n, t_min, device, prim.ctypes.data, t.ctypes.data),
+           "closest_hit")
+        return prim, t
+
+    def texture_value(self, world, tex, uvp: np.ndarray, device=0):
+        q = np.ascontiguousarray(uvp, dtype=np.float64)
+        out = np.empty((q.shape[0], 3), np.float32)
+        _h(lib.rtb_debug_texture_value(self._p, world, tex, q.ctypes.data, q.shape[0], device, out.ctypes.data),
+           "texture_value")
+        return out
+
+
+def resolve_device(d_sum_ptr: int, nx, ny, ns, d_rgb8_ptr: int, stream: int = 0):
+    _h(lib.rtb_resolve_device(d_sum_ptr, nx, ny, ns, d_rgb8_ptr, stream), "resolve_device")
+
+
+def primary_rays(cam, nx, ny, sample=0, seed=1) -> np.ndarray:
+    out = np.empty((nx * ny, 7), np.float64)
+    _h(lib.rtb_primary_rays(C.byref(cam), nx, ny, sample, seed, out.ctypes.data), "primary_rays")
+    return out
+
+
+def ppm_p3(rgb8: np.ndarray) -> bytes:
+    a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    ny, nx = a.shape[0], a.shape[1]
+    n = lib.rtb_ppm_p3(a.ctypes.data, nx, ny, None, 0)
+    buf = C.create_string_buffer(n + 1)
+    lib.rtb_ppm_p3(a.ctypes.data, nx, ny, buf, n + 1)
+    return buf.raw[:n]
+
+
+def create_image(ny, nx, ns, cam, scene: Scene, world: int, opts=None) -> bytes:
+    """create_image(ny, nx, ns, cam, world) -> String (tests/test.rs:55): same argument order,
+    same P3 text; the pixel loop runs on the GPU."""
+    _, rgb8, _ = scene.render(world, cam, nx, ny, ns, opts, want_sum=False)
+    return ppm_p3(rgb8)

@@ -1,0 +1,31 @@
+// flatten.hpp — object graph -> flat device tables (host side, no CUDA).
+#pragma once
+#include <string>
+#include <vector>
+
+#include "device_types.h"
+#include "scene.hpp"
+
+namespace rtb {
+
+struct FlatScene {
+  std::vector<DNode> nodes;
+  std::vector<DPrim> prims;   // BVH leaf order
+  std::vector<DPrim> bprims;  // medium boundaries, grouped per medium
+  std::vector<DMedium> media;
+  std::vector<DXform> xforms;  // [0] = identity
+  std::vector<DMaterial> mats;
+  std::vector<DTexture> texs;
+  std::vector<DPerlin> perlin;
+  std::vector<uint32_t> texels;
+  int root = -1;
+  int n_prim_ids = 0;
+  int bvh_depth = 0;
+  double time_lo = 0.0, time_hi = 1.0;  // shutter range the moving-sphere bounds cover
+  bool has_moving = false;
+};
+
+// Returns 0 or an RtbStatus error (message via set_error).
+int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi, FlatScene* out);
+
+}  // namespace rtb

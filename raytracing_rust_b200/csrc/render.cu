@@ -1,0 +1,556 @@
+// render.cu — sm_100a kernels and the render half of the C ABI (include/rtb200.h).
+//
+// Replaces the reference's pixel loop and radiance recursion:
+//   create_image  tests/test.rs:55-85   (per-pixel sample loop, gamma, quantisation)
+//   color         src/color.rs:6-23     (emitted + attenuation * color(scattered), depth < 50)
+//
+// Kernels in this file
+//   k_render_mega   persistent per-thread path loop with regeneration: a thread owns one pixel
+//                   (or one sample slice of it), runs one ray segment per loop iteration and
+//                   starts its next camera sample as soon as a path ends, so a warp only idles
+//                   in the tail of its sample budget.  Radiance sums stay in registers and are
+//                   added to the accumulation buffer once per launch.
+//   k_closest_hit   primary-ray closest-hit query for the primitive-ID parity test.
+//   k_resolve       /ns, sqrt, clamp, 255.99 truncation (tests/test.rs:71-78).
+//   k_texture_eval  Texture::value over a batch (parity tests).
+// The wavefront pipeline lives in wavefront.cu.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "flatten.hpp"
+#include "render_internal.hpp"
+#include "trace.cuh"
+
+namespace rtb {
+
+// ================================ device code ==================================================
+
+struct MegaParams {
+  int nx, ny;
+  int ns;             // total samples per pixel of the image (for the s < ns bound)
+  int sample_first;   // first sample index this launch renders
+  int sample_step;    // distance between consecutive samples of this launch (GPU sharding stride)
+  int sample_count;   // samples per pixel in this launch
+  int slices;         // threads per pixel (sample slices) in this launch
+  int max_depth;
+  float t_min;
+  int background;
+  uint64_t seed;
+};
+
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <bool kStats>
+__global__ void __launch_bounds__(256) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
+                                                     unsigned long long* __restrict__ stats) {
+  // warp -> 8x4 pixel tile, so the 32 camera rays of a warp start out coherent
+  const int lane = threadIdx.x & 31;
+  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int tiles_x = (P.nx + 7) >> 3, tiles_y = (P.ny + 3) >> 2;
+  const long long tile = warp_global / P.slices;
+  const int slice = (int)(warp_global - tile * P.slices);
+  const int tx = (int)(tile % tiles_x), ty = (int)(tile / tiles_x);
+  const int i = tx * 8 + (lane & 7);
+  const int row = ty * 4 + (lane >> 3);  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
+  const bool valid = ty < tiles_y && i < P.nx && row < P.ny;
+  const int j = P.ny - 1 - row;
+  const uint32_t pixel = (uint32_t)(row * P.nx + i);
+
+  Counters cnt = {0, 0, 0};
+  TexCounters tc = {{0, 0, 0, 0}};
+  unsigned long long n_paths = 0, n_segments = 0;
+  unsigned long long n_shade[5] = {0, 0, 0, 0, 0};
+
+  V3f sum = mk(0.f, 0.f, 0.f);
+  if (valid) {
+    int k = slice;  // index into this launch's sample list; this thread takes k, k+slices, ...
+    bool alive = false;
+    RayF ray;
+    V3f thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
+    int depth = 0, self_prim = -1, self_face = 0;
+    PathRng rng;
+    rng.n = 0;
+    for (;;) {
+      if (!alive) {
+        if (k >= P.sample_count) break;
+        const int s = P.sample_first + k * P.sample_step;
+        k += P.slices;
+        rng.init(P.seed, pixel, (uint32_t)s, 0u);
+        ray = camera_ray(cam, i, j, P.nx, P.ny, rng);
+        thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
+        depth = 0, self_prim = -1, self_face = 0;
+        alive = true;
+        if (kStats) n_paths++;
+      }
+      // ---- one segment: world.hit(ray, t_min, MAX)  (src/color.rs:7)
+      n_segments++;
+      Hit h = trace_closest<kStats>(sv, ray, P.t_min, self_prim, self_face, &cnt);
+      int medium = -1;
+      if (sv.n_media > 0) medium = sample_media<kStats>(sv, ray, P.t_min, &h.t, rng, &cnt);
+      if (medium < 0 && h.prim < 0) {  // miss
+        V3f bg = background_color(P.background, ray.d);
+        rad = rad + thr * bg;
+        sum = sum + rad;
+        alive = false;
+        continue;
+      }
+      Surface s;
+      if (medium >= 0) {  // src/medium.rs:44-51
+        s.p = madd(h.t, ray.d, ray.o);
+        s.n = mk(1.f, 0.f, 0.f);
+        s.u = 0.f, s.v = 0.f;
+        s.mat = __ldg(&sv.media[medium].mat);
+        self_prim = -1;
+      } else {
+        s = finalize_hit(sv, sv.prims, ray, h);
+        self_prim = h.prim, self_face = h.face;
+      }
+      const int4 m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
+      if (kStats) n_shade[m.x]++;
+      if (m.x == RTB_MAT_DIFFUSE_LIGHT)  // emitted, src/color.rs:8 (zero for every other material)
+        rad = rad + thr * texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
+      V3f atten;
+      if (depth < P.max_depth && scatter<kStats>(sv, m.x, m.y, __int_as_float(m.z), s, ray, rng, &atten, &tc)) {
+        thr = thr * atten;
+        ++depth;
+      } else {
+        sum = sum + rad;
+        alive = false;
+      }
+    }
+    float* a = accum + 3ull * pixel;
+    atomicAdd(a, sum.x);
+    atomicAdd(a + 1, sum.y);
+    atomicAdd(a + 2, sum.z);
+  }
+  // counters: one atomic per warp
+  unsigned long long v = warp_sum(n_segments);
+  if (lane == 0 && v) atomicAdd(stats + 1, v);
+  if (kStats) {
+    unsigned long long vals[14] = {n_paths,    0,          cnt.node_tests, cnt.prim_tests, cnt.medium_tests,
+                                   n_shade[0], n_shade[1], n_shade[2],     n_shade[3],     n_shade[4],
+                                   tc.n[0],    tc.n[1],    tc.n[2],        tc.n[3]};
+#pragma unroll
+    for (int q = 0; q < 14; ++q) {
+      if (q == 1) continue;
+      unsigned long long w = warp_sum(vals[q]);
+      if (lane == 0 && w) atomicAdd(stats + q, w);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_closest_hit(SceneView sv, const float* __restrict__ rays, size_t n, float t_min,
+                                                     int* __restrict__ out_prim, float* __restrict__ out_t) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const float* r = rays + 7 * idx;
+  RayF ray;
+  ray.o = mk(r[0], r[1], r[2]);
+  ray.d = mk(r[3], r[4], r[5]);
+  ray.time = r[6];
+  Counters cnt;
+  Hit h = trace_closest<false>(sv, ray, t_min, -1, 0, &cnt);
+  int id = -1;
+  if (h.prim >= 0) {
+    const int4 C = ldg4i(&sv.prims[h.prim].c);
+    id = C.z + (RTB_PRIM_TYPE(C.x) == DP_BOX ? h.face : 0);
+  }
+  out_prim[idx] = id;
+  out_t[idx] = h.prim >= 0 ? h.t : 0.0f;
+}
+
+// tests/test.rs:71-78: col /= ns; c = clamp(sqrt(c), 0, 1); (255.99 * c) as i32
+__global__ void k_resolve(const float* __restrict__ sum, size_t n_values, float inv_ns, uint8_t* __restrict__ rgb8) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n_values) return;
+  float c = sqrtf(sum[idx] * inv_ns);
+  c = c > 1.0f ? 1.0f : (c < 0.0f ? 0.0f : c);  // NaN passes through, then `as i32` -> 0
+  float q = 255.99f * c;
+  int v = (q != q) ? 0 : (int)q;
+  rgb8[idx] = (uint8_t)min(max(v, 0), 255);
+}
+
+__global__ void k_texture_eval(SceneView sv, int tex, const float* __restrict__ uvp, size_t n, float* __restrict__ out) {
+  size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n) return;
+  const float* q = uvp + 5 * idx;
+  TexCounters tc;
+  V3f c = texture_value<false>(sv, tex, q[0], q[1], mk(q[2], q[3], q[4]), &tc);
+  out[3 * idx] = c.x, out[3 * idx + 1] = c.y, out[3 * idx + 2] = c.z;
+}
+
+// ================================ host code ====================================================
+
+#define CUDA_TRY(expr)                                                                            \
+  do {                                                                                            \
+    cudaError_t e_ = (expr);                                                                      \
+    if (e_ != cudaSuccess)                                                                        \
+      return fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? RTB_ERR_NO_DEVICE : RTB_ERR_CUDA, \
+                  std::string(#expr) + ": " + cudaGetErrorString(e_));                          \
+  } while (0)
+
+void destroy_device_scene(DeviceScene* d) {
+  if (!d) return;
+  int prev = 0;
+  cudaGetDevice(&prev);
+  cudaSetDevice(d->device);
+  for (void* p : d->allocs) cudaFree(p);
+  if (d->wf) destroy_wavefront_state(d->wf);
+  cudaSetDevice(prev);
+  delete d;
+}
+
+template <class T>
+static int upload_vec(DeviceScene* d, const std::vector<T>& v, const T** out) {
+  void* p = nullptr;
+  size_t bytes = std::max<size_t>(v.size() * sizeof(T), 16);
+  CUDA_TRY(cudaMalloc(&p, bytes));
+  d->allocs.push_back(p);
+  if (!v.empty()) CUDA_TRY(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *out = (const T*)p;
+  return RTB_OK;
+}
+
+int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi) {
+  if (!s) return fail(RTB_ERR_INVALID, "null scene");
+  if (world < 0) world = s->dev_world;
+  if (!s->obj_ok(world)) return fail(RTB_ERR_INVALID, "bad world handle");
+  if (s->dev && s->dev_world == world && s->dev->device == device &&
+      (!s->dev->flat.has_moving || (s->dev->flat.time_lo <= tlo && s->dev->flat.time_hi >= thi)))
+    return RTB_OK;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(RTB_ERR_NO_DEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count = 0"));
+  if (device < 0 || device >= ndev) return fail(RTB_ERR_INVALID, "bad device ordinal");
+  if (s->dev) {
+    tlo = std::min(tlo, s->dev->flat.time_lo), thi = std::max(thi, s->dev->flat.time_hi);
+    destroy_device_scene(s->dev);
+    s->dev = nullptr;
+  }
+  DeviceScene* d = new DeviceScene();
+  d->device = device;
+  int rc = flatten_scene(*s, world, tlo, thi, &d->flat);
+  if (rc != RTB_OK) {
+    delete d;
+    return rc;
+  }
+  CUDA_TRY(cudaSetDevice(device));
+  SceneView& v = d->view;
+  const FlatScene& f = d->flat;
+  if ((rc = upload_vec(d, f.nodes, &v.nodes)) || (rc = upload_vec(d, f.prims, &v.prims)) ||
+      (rc = upload_vec(d, f.bprims, &v.bprims)) || (rc = upload_vec(d, f.media, &v.media)) ||
+      (rc = upload_vec(d, f.xforms, &v.xforms)) || (rc = upload_vec(d, f.mats, &v.mats)) ||
+      (rc = upload_vec(d, f.texs, &v.texs)) || (rc = upload_vec(d, f.perlin, &v.perlin)) ||
+      (rc = upload_vec(d, f.texels, &v.texels))) {
+    destroy_device_scene(d);
+    return rc;
+  }
+  v.n_nodes = (int)f.nodes.size(), v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
+  v.root = f.root;
+  void* st = nullptr;
+  CUDA_TRY(cudaMalloc(&st, 32 * sizeof(unsigned long long)));
+  d->allocs.push_back(st);
+  d->d_stats = (unsigned long long*)st;
+  CUDA_TRY(cudaGetDeviceProperties(&d->prop, device));
+  s->dev = d;
+  s->dev_world = world;
+  return RTB_OK;
+}
+
+// Camera::new, src/camera.rs:21-51, evaluated in f64 on the host and narrowed to f32.
+void make_device_camera(const RtbCamera& c, DCamera* out) {
+  auto sub = [](const double* a, const double* b, double* r) { for (int i = 0; i < 3; ++i) r[i] = a[i] - b[i]; };
+  auto nrm = [](double* a) {
+    double n = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+    for (int i = 0; i < 3; ++i) a[i] /= n;
+  };
+  auto crs = [](const double* a, const double* b, double* r) {
+    r[0] = a[1] * b[2] - a[2] * b[1], r[1] = a[2] * b[0] - a[0] * b[2], r[2] = a[0] * b[1] - a[1] * b[0];
+  };
+  double theta = c.vertical_fov * M_PI / 180.0;
+  double half_height = c.focus_dist * std::tan(theta / 2.0);
+  double half_width = c.aspect * half_height;
+  double w[3], u[3], v[3];
+  sub(c.look_from, c.look_at, w);
+  nrm(w);
+  crs(c.view_up, w, u);
+  nrm(u);
+  crs(w, u, v);
+  for (int i = 0; i < 3; ++i) {
+    out->origin[i] = (float)c.look_from[i];
+    out->llc[i] = (float)(c.look_from[i] - half_width * u[i] - half_height * v[i] - c.focus_dist * w[i]);
+    out->horizontal[i] = (float)(2.0 * half_width * u[i]);
+    out->vertical[i] = (float)(2.0 * half_height * v[i]);
+    out->u[i] = (float)u[i];
+    out->v[i] = (float)v[i];
+  }
+  out->time0 = (float)c.time0, out->time1 = (float)c.time1;
+  out->lens_radius = (float)(c.aperture / 2.0);
+}
+
+static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
+                       cudaStream_t stream, uint64_t* launches) {
+  const int stride = std::max(1, o.sample_stride);
+  const int begin = std::max(0, o.sample_begin);
+  const int my_samples = begin < ns ? (ns - begin + stride - 1) / stride : 0;
+  const long long tiles = (long long)((nx + 7) / 8) * ((ny + 3) / 4);
+  // enough resident warps to fill the machine: split a pixel's samples over several threads
+  // when the image alone does not supply ~2 waves of warps
+  const long long want_warps = (long long)d->prop.multiProcessorCount * 64 * 2;
+  const int chunk_max = 64;  // samples per pixel per launch: bounds kernel duration
+  for (int done = 0; done < my_samples; done += chunk_max) {
+    MegaParams P;
+    P.nx = nx, P.ny = ny, P.ns = ns;
+    P.sample_count = std::min(chunk_max, my_samples - done);
+    P.sample_first = begin + done * stride;
+    P.sample_step = stride;
+    int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
+    P.slices = std::max(1, slices);
+    P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
+    const long long warps = tiles * P.slices;
+    const int block = 256;
+    const long long blocks = (warps * 32 + block - 1) / block;
+    if (o.collect_stats)
+      k_render_mega<true><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+    else
+      k_render_mega<false><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+    ++*launches;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return RTB_OK;
+}
+
+}  // namespace rtb
+
+using namespace rtb;
+
+extern "C" {
+
+int rtb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+void rtb_render_opts_default(rtb_render_opts* o) {
+  if (!o) return;
+  std::memset(o, 0, sizeof *o);
+  o->max_depth = 50;   // src/color.rs:9
+  o->t_min = 0.001;    // src/color.rs:7
+  o->background = RTB_BG_BLACK;
+  o->seed = 1;
+  o->sample_begin = 0, o->sample_stride = 1;
+  o->pipeline = RTB_PIPE_AUTO;
+}
+
+int rtb_scene_upload(rtb_scene* s, int world, int device) { return ensure_uploaded(s, world, device, 0.0, 1.0); }
+
+int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int ns, const rtb_render_opts* opts,
+                      float* d_sum_rgb, void* cuda_stream, rtb_stats* stats) {
+  if (!s || !camera || !opts || !d_sum_rgb || nx <= 0 || ny <= 0 || ns < 0)
+    return fail(RTB_ERR_INVALID, "render_device: bad argument");
+  if (!s->dev) return fail(RTB_ERR_INVALID, "render_device: scene not uploaded (rtb_scene_upload)");
+  int rc = ensure_uploaded(s, s->dev_world, s->dev->device, std::min(camera->time0, camera->time1),
+                           std::max(camera->time0, camera->time1));
+  if (rc != RTB_OK) return rc;
+  DeviceScene* d = s->dev;
+  CUDA_TRY(cudaSetDevice(d->device));
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  DCamera cam;
+  make_device_camera(*camera, &cam);
+  uint64_t launches = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (stats) {
+    CUDA_TRY(cudaMemsetAsync(d->d_stats, 0, 32 * sizeof(unsigned long long), stream));
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    CUDA_TRY(cudaEventRecord(e0, stream));
+  }
+  int pipe = opts->pipeline;
+  if (pipe == RTB_PIPE_AUTO) pipe = RTB_PIPE_MEGAKERNEL;
+  if (pipe == RTB_PIPE_WAVEFRONT)
+    rc = launch_wavefront(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
+  else
+    rc = launch_mega(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
+  if (rc != RTB_OK) return rc;
+  if (stats) {
+    CUDA_TRY(cudaEventRecord(e1, stream));
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float ms = 0;
+    CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    unsigned long long h[32];
+    CUDA_TRY(cudaMemcpy(h, d->d_stats, sizeof h, cudaMemcpyDeviceToHost));
+    std::memset(stats, 0, sizeof *stats);
+    const int stride = std::max(1, opts->sample_stride), begin = std::max(0, opts->sample_begin);
+    const uint64_t my_samples = begin < ns ? (uint64_t)(ns - begin + stride - 1) / stride : 0;
+    stats->paths = my_samples * (uint64_t)nx * ny;
+    stats->segments = h[1];
+    stats->node_tests = h[2], stats->prim_tests = h[3], stats->medium_tests = h[4];
+    for (int i = 0; i < 5; ++i) stats->shade[i] = h[5 + i];
+    for (int i = 0; i < 4; ++i) stats->tex_evals[i] = h[10 + i];
+    stats->kernel_launches = launches;
+    stats->device_ms = ms;
+  }
+  return RTB_OK;
+}
+
+int rtb_resolve_device(const float* d_sum_rgb, int nx, int ny, int ns, uint8_t* d_rgb8, void* cuda_stream) {
+  if (!d_sum_rgb || !d_rgb8 || nx <= 0 || ny <= 0 || ns <= 0) return fail(RTB_ERR_INVALID, "resolve_device: bad argument");
+  size_t n = (size_t)3 * nx * ny;
+  k_resolve<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)cuda_stream>>>(d_sum_rgb, n, 1.0f / (float)ns, d_rgb8);
+  CUDA_TRY(cudaGetLastError());
+  return RTB_OK;
+}
+
+int rtb_render(rtb_scene* s, int world, const RtbCamera* camera, int nx, int ny, int ns, const rtb_render_opts* opts,
+               float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats* stats) {
+  if (!s || !camera || nx <= 0 || ny <= 0 || ns <= 0) return fail(RTB_ERR_INVALID, "render: bad argument");
+  rtb_render_opts o;
+  if (opts) o = *opts; else rtb_render_opts_default(&o);
+  int rc = ensure_uploaded(s, world, o.device, std::min(camera->time0, camera->time1), std::max(camera->time0, camera->time1));
+  if (rc != RTB_OK) return rc;
+  CUDA_TRY(cudaSetDevice(o.device));
+  const size_t n = (size_t)3 * nx * ny;
+  float* d_sum = nullptr;
+  uint8_t* d_rgb8 = nullptr;
+  CUDA_TRY(cudaMalloc(&d_sum, n * sizeof(float)));
+  auto cleanup = [&]() {
+    cudaFree(d_sum);
+    if (d_rgb8) cudaFree(d_rgb8);
+  };
+  cudaError_t e = cudaMemsetAsync(d_sum, 0, n * sizeof(float), 0);
+  if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+  rc = rtb_render_device(s, camera, nx, ny, ns, &o, d_sum, nullptr, stats);
+  if (rc != RTB_OK) { cleanup(); return rc; }
+  if (out_rgb8) {
+    e = cudaMalloc(&d_rgb8, n);
+    if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+    rc = rtb_resolve_device(d_sum, nx, ny, ns, d_rgb8, nullptr);
+    if (rc != RTB_OK) { cleanup(); return rc; }
+    e = cudaMemcpy(out_rgb8, d_rgb8, n, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+  }
+  if (out_sum_rgb) {
+    e = cudaMemcpy(out_sum_rgb, d_sum, n * sizeof(float), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+  }
+  e = cudaDeviceSynchronize();
+  cleanup();
+  if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
+  return RTB_OK;
+}
+
+int rtb_closest_hit(rtb_scene* s, int world, const double* rays, size_t n, double t_min, int device, int32_t* out_prim,
+                    float* out_t) {
+  if (!s || (n && (!rays || !out_prim))) return fail(RTB_ERR_INVALID, "closest_hit: bad argument");
+  double tlo = 0.0, thi = 1.0;
+  for (size_t i = 0; i < n; ++i) tlo = std::min(tlo, rays[7 * i + 6]), thi = std::max(thi, rays[7 * i + 6]);
+  int rc = ensure_uploaded(s, world, device, tlo, thi);
+  if (rc != RTB_OK) return rc;
+  if (n == 0) return RTB_OK;
+  CUDA_TRY(cudaSetDevice(device));
+  std::vector<float> h((size_t)7 * n);
+  for (size_t i = 0; i < 7 * n; ++i) h[i] = (float)rays[i];
+  float *d_rays = nullptr, *d_t = nullptr;
+  int* d_prim = nullptr;
+  CUDA_TRY(cudaMalloc(&d_rays, h.size() * sizeof(float)));
+  CUDA_TRY(cudaMalloc(&d_t, n * sizeof(float)));
+  CUDA_TRY(cudaMalloc(&d_prim, n * sizeof(int)));
+  CUDA_TRY(cudaMemcpy(d_rays, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  k_closest_hit<<<(unsigned)((n + 255) / 256), 256>>>(s->dev->view, d_rays, n, (float)t_min, d_prim, d_t);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(out_prim, d_prim, n * sizeof(int), cudaMemcpyDeviceToHost));
+  if (out_t) CUDA_TRY(cudaMemcpy(out_t, d_t, n * sizeof(float), cudaMemcpyDeviceToHost));
+  cudaFree(d_rays), cudaFree(d_t), cudaFree(d_prim);
+  return RTB_OK;
+}
+
+// Texture::value over a batch on the device (parity tests): uvp = n x {u,v,px,py,pz} (host,
+// double), out = n x {r,g,b} (host, float)
+int rtb_debug_texture_value(rtb_scene* s, int world, int tex, const double* uvp, size_t n, int device, float* out) {
+  if (!s || !uvp || !out || !s->tex_ok(tex)) return fail(RTB_ERR_INVALID, "texture_value: bad argument");
+  int rc = ensure_uploaded(s, world, device, 0.0, 1.0);
+  if (rc != RTB_OK) return rc;
+  CUDA_TRY(cudaSetDevice(device));
+  std::vector<float> h((size_t)5 * n);
+  for (size_t i = 0; i < 5 * n; ++i) h[i] = (float)uvp[i];
+  float *d_in = nullptr, *d_out = nullptr;
+  CUDA_TRY(cudaMalloc(&d_in, h.size() * sizeof(float) + 16));
+  CUDA_TRY(cudaMalloc(&d_out, 3 * n * sizeof(float) + 16));
+  CUDA_TRY(cudaMemcpy(d_in, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  if (n) k_texture_eval<<<(unsigned)((n + 255) / 256), 256>>>(s->dev->view, tex, d_in, n, d_out);
+  CUDA_TRY(cudaGetLastError());
+  CUDA_TRY(cudaMemcpy(out, d_out, 3 * n * sizeof(float), cudaMemcpyDeviceToHost));
+  cudaFree(d_in), cudaFree(d_out);
+  return RTB_OK;
+}
+
+// Camera::get_ray for the fixed parity batch, on the host in f64, from the same Philox draws
+// the kernels use (trace.cuh camera_ray): ray i = sample `sidx` of pixel i.
+int rtb_primary_rays(const RtbCamera* c, int nx, int ny, int sidx, uint64_t seed, double* out) {
+  if (!c || !out || nx <= 0 || ny <= 0) return fail(RTB_ERR_INVALID, "primary_rays: bad argument");
+  auto sub = [](const double* a, const double* b, double* r) { for (int i = 0; i < 3; ++i) r[i] = a[i] - b[i]; };
+  auto nrm = [](double* a) {
+    double n = std::sqrt(a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+    for (int i = 0; i < 3; ++i) a[i] /= n;
+  };
+  auto crs = [](const double* a, const double* b, double* r) {
+    r[0] = a[1] * b[2] - a[2] * b[1], r[1] = a[2] * b[0] - a[0] * b[2], r[2] = a[0] * b[1] - a[1] * b[0];
+  };
+  double theta = c->vertical_fov * M_PI / 180.0;
+  double half_height = c->focus_dist * std::tan(theta / 2.0);
+  double half_width = c->aspect * half_height;
+  double w[3], u[3], v[3], llc[3], hor[3], ver[3];
+  sub(c->look_from, c->look_at, w);
+  nrm(w);
+  crs(c->view_up, w, u);
+  nrm(u);
+  crs(w, u, v);
+  for (int i = 0; i < 3; ++i) {
+    llc[i] = c->look_from[i] - half_width * u[i] - half_height * v[i] - c->focus_dist * w[i];
+    hor[i] = 2.0 * half_width * u[i];
+    ver[i] = 2.0 * half_height * v[i];
+  }
+  const double lens_radius = c->aperture / 2.0;
+  const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  for (int row = 0; row < ny; ++row) {
+    const int j = ny - 1 - row;
+    for (int i = 0; i < nx; ++i) {
+      const uint32_t pixel = (uint32_t)(row * nx + i);
+      u4 b0 = philox4x32_10(u4{0u, pixel, (uint32_t)sidx, 0u}, k0, k1);
+      u4 b1 = philox4x32_10(u4{1u, pixel, (uint32_t)sidx, 0u}, k0, k1);
+      double ju = u01(b0.x), jv = u01(b0.y), lr = u01(b0.z), lp = u01(b0.w), xt = u01(b1.x);
+      double sx = ((double)i + ju) / (double)nx, ty = ((double)j + jv) / (double)ny;
+      double org[3] = {c->look_from[0], c->look_from[1], c->look_from[2]};
+      if (lens_radius != 0.0) {
+        double r = lens_radius * std::sqrt(lr), phi = (2.0 * lp - 1.0) * M_PI;
+        double rx = r * std::cos(phi), ry = r * std::sin(phi);
+        for (int q = 0; q < 3; ++q) org[q] += u[q] * rx + v[q] * ry;
+      }
+      double* o = out + 7 * (size_t)pixel;
+      for (int q = 0; q < 3; ++q) {
+        o[q] = org[q];
+        o[3 + q] = llc[q] + sx * hor[q] + ty * ver[q] - org[q];
+      }
+      o[6] = c->time0 + xt * (c->time1 - c->time0);
+    }
+  }
+  return RTB_OK;
+}
+
+}  // extern "C"

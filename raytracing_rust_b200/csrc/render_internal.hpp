@@ -1,0 +1,31 @@
+// render_internal.hpp — host-side state shared by render.cu and wavefront.cu (internal).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <vector>
+
+#include "device_types.h"
+#include "flatten.hpp"
+#include "rtb200.h"
+
+namespace rtb {
+
+struct WavefrontState;  // wavefront.cu
+void destroy_wavefront_state(WavefrontState*);
+
+struct DeviceScene {
+  int device = 0;
+  FlatScene flat;   // host copy of what was uploaded (bounds, counts)
+  SceneView view{};  // device pointers
+  std::vector<void*> allocs;
+  unsigned long long* d_stats = nullptr;  // 32 counters
+  cudaDeviceProp prop{};
+  WavefrontState* wf = nullptr;
+};
+
+int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi);
+void make_device_camera(const RtbCamera& c, DCamera* out);
+int launch_wavefront(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
+                     cudaStream_t stream, uint64_t* launches);
+
+}  // namespace rtb

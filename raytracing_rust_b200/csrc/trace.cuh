@@ -1,0 +1,612 @@
+// trace.cuh — device-side building blocks shared by the megakernel and the wavefront
+// kernels: RNG stream, ray/primitive intersection, BVH traversal, constant media, textures
+// and material scattering.  f32 throughout; each routine cites the f64 reference code whose
+// result it reproduces.
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "device_types.h"
+#include "philox.h"
+#include "rtb_scene_format.h"
+
+namespace rtb {
+
+// ---------------------------------------------------------------------------------------------
+struct V3f {
+  float x, y, z;
+};
+__device__ __forceinline__ V3f mk(float x, float y, float z) { return V3f{x, y, z}; }
+__device__ __forceinline__ V3f operator+(V3f a, V3f b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3f operator-(V3f a, V3f b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3f operator-(V3f a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ V3f operator*(float s, V3f a) { return mk(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ V3f operator*(V3f a, V3f b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float dot(V3f a, V3f b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+__device__ __forceinline__ V3f madd(float t, V3f d, V3f o) {  // o + t*d
+  return mk(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
+}
+__device__ __forceinline__ float comp(V3f v, int axis) { return axis == 0 ? v.x : (axis == 1 ? v.y : v.z); }
+__device__ __forceinline__ void set_comp(V3f& v, int axis, float s) {
+  if (axis == 0) v.x = s;
+  else if (axis == 1) v.y = s;
+  else v.z = s;
+}
+
+__device__ __forceinline__ float4 ldg4(const f4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ int4 ldg4i(const i4* p) { return __ldg(reinterpret_cast<const int4*>(p)); }
+
+// ---- RNG stream of one path -------------------------------------------------------------------
+struct PathRng {
+  uint32_t k0, k1, pixel, sample;
+  uint32_t n;  // draws consumed so far
+  u4 buf;
+  __device__ __forceinline__ void init(uint64_t seed, uint32_t pixel_, uint32_t sample_, uint32_t n0) {
+    k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32), pixel = pixel_, sample = sample_;
+    n = n0;
+    if (n0 & 3u) buf = philox4x32_10(u4{n0 >> 2, pixel, sample, 0u}, k0, k1);
+  }
+  __device__ __forceinline__ float next() {
+    uint32_t i = n & 3u;
+    if (i == 0u) buf = philox4x32_10(u4{n >> 2, pixel, sample, 0u}, k0, k1);
+    ++n;
+    uint32_t r = i == 0u ? buf.x : (i == 1u ? buf.y : (i == 2u ? buf.z : buf.w));
+    return u01(r);
+  }
+};
+
+// uniform in the unit ball == the distribution of the rejection loop at src/util.rs:4-13,
+// sampled directly (3 draws, no divergence)
+__device__ __forceinline__ V3f sample_unit_ball(PathRng& rng) {
+  float z = 1.0f - 2.0f * rng.next();
+  float phi = (2.0f * rng.next() - 1.0f) * CUDART_PI_F;
+  float r = cbrtf(rng.next());
+  float s = sqrtf(fmaxf(0.0f, 1.0f - z * z)) * r;
+  float sn, cs;
+  __sincosf(phi, &sn, &cs);
+  return mk(s * cs, s * sn, r * z);
+}
+
+// ---- rays -----------------------------------------------------------------------------------
+struct RayF {
+  V3f o, d;
+  float time;
+};
+
+struct Hit {
+  float t;
+  int prim;  // index into prims (or bprims for boundary queries); -1 = none
+  int face;  // BOX: face 0..5 in the order of src/cube.rs:21-74
+};
+
+__device__ __forceinline__ V3f xf_point(const DXform& x, V3f p) {  // local = M p + b
+  return mk(fmaf(x.m[0], p.x, fmaf(x.m[1], p.y, fmaf(x.m[2], p.z, x.b[0]))),
+            fmaf(x.m[3], p.x, fmaf(x.m[4], p.y, fmaf(x.m[5], p.z, x.b[1]))),
+            fmaf(x.m[6], p.x, fmaf(x.m[7], p.y, fmaf(x.m[8], p.z, x.b[2]))));
+}
+__device__ __forceinline__ V3f xf_vec(const DXform& x, V3f v) {  // M v
+  return mk(fmaf(x.m[0], v.x, fmaf(x.m[1], v.y, x.m[2] * v.z)), fmaf(x.m[3], v.x, fmaf(x.m[4], v.y, x.m[5] * v.z)),
+            fmaf(x.m[6], v.x, fmaf(x.m[7], v.y, x.m[8] * v.z)));
+}
+__device__ __forceinline__ V3f xf_vec_t(const DXform& x, V3f v) {  // M^T v
+  return mk(fmaf(x.m[0], v.x, fmaf(x.m[3], v.y, x.m[6] * v.z)), fmaf(x.m[1], v.x, fmaf(x.m[4], v.y, x.m[7] * v.z)),
+            fmaf(x.m[2], v.x, fmaf(x.m[5], v.y, x.m[8] * v.z)));
+}
+__device__ __forceinline__ V3f xf_point_inv(const DXform& x, V3f p) {  // world = M^T (p - b)
+  return xf_vec_t(x, mk(p.x - x.b[0], p.y - x.b[1], p.z - x.b[2]));
+}
+
+__device__ __forceinline__ DXform load_xform(const DXform* xs, int i) {
+  DXform x;
+  const float4* p = reinterpret_cast<const float4*>(xs + i);
+  float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+  x.m[0] = a.x, x.m[1] = a.y, x.m[2] = a.z, x.m[3] = a.w;
+  x.m[4] = b.x, x.m[5] = b.y, x.m[6] = b.z, x.m[7] = b.w;
+  x.m[8] = c.x;
+  x.b[0] = c.y, x.b[1] = c.z, x.b[2] = c.w;
+  return x;
+}
+
+__device__ __forceinline__ V3f sphere_center(float4 a, float4 b, int4 c, float time) {
+  // MovingSphere::center, src/sphere.rs:115-118
+  V3f ctr = mk(a.x, a.y, a.z);
+  if (RTB_PRIM_TYPE(c.x) == DP_MOVING_SPHERE) {
+    float f = (time - b.w) * __int_as_float(c.w);
+    ctr = madd(f, mk(b.x, b.y, b.z), ctr);
+  }
+  return ctr;
+}
+
+struct Counters {
+  unsigned long long node_tests, prim_tests, medium_tests;
+};
+
+// One primitive against one ray over (t_min, t_max).  `self` means the ray origin lies ON this
+// primitive (it is the scattering surface): in exact arithmetic that root is t = 0 < t_min, so
+// it is excluded analytically instead of trusting f32 round-off against t_min = 1e-3.
+//   Sphere: src/sphere.rs:37-77 (strict t_min < t < t_max, near root first), with the
+//           closest-approach form t = tc -/+ h, h^2 = (r^2 - |oc + tc d|^2)/a, which does not
+//           cancel for the r = 1000 / r = 5000 spheres the way b^2 - a c does in f32.
+//   Rect:   src/rect.rs:39-69 (all comparisons inclusive).
+//   Box:    the six Rects of src/cube.rs:21-74 scanned by HittableList::hit == nearest of
+//           {slab entry, slab exit} inside [t_min, t_max].
+template <bool kStats>
+__device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXform* __restrict__ xforms,
+                                               const RayF& ray, float inv_a, float t_min, float t_max, bool self,
+                                               int self_face, float* t_out, int* face_out, Counters* cnt) {
+  if (kStats) cnt->prim_tests++;
+  const float4 A = ldg4(&prims[pi].a);
+  const float4 B = ldg4(&prims[pi].b);
+  const int4 C = ldg4i(&prims[pi].c);
+  const int type = RTB_PRIM_TYPE(C.x);
+  if (type <= DP_MOVING_SPHERE) {
+    V3f ctr = sphere_center(A, B, C, ray.time);
+    V3f oc = ray.o - ctr;
+    float b = dot(oc, ray.d);
+    float tc = -b * inv_a;
+    float t;
+    if (self) {
+      t = 2.0f * tc;  // roots are 0 and -2b/a
+      if (t < t_max && t > t_min) { *t_out = t; return true; }
+      return false;
+    }
+    V3f l = madd(tc, ray.d, oc);
+    float disc = fmaf(A.w, A.w, -dot(l, l));
+    if (disc > 0.0f) {
+      float h = sqrtf(disc * inv_a);
+      t = tc - h;
+      if (t < t_max && t > t_min) { *t_out = t; return true; }
+      t = tc + h;
+      if (t < t_max && t > t_min) { *t_out = t; return true; }
+    }
+    return false;
+  }
+  // planar primitives live in the local space of their instance transform
+  V3f o = ray.o, d = ray.d;
+  const int xi = RTB_PRIM_XFORM(C.x);
+  if (xi != 0) {
+    DXform x = load_xform(xforms, xi);
+    o = xf_point(x, ray.o);
+    d = xf_vec(x, ray.d);
+  }
+  if (type == DP_RECT) {
+    if (self) return false;  // a ray leaving a plane never meets it again
+    const int plane = RTB_PRIM_PLANE(C.x);
+    const int k_axis = plane, a_axis = plane == 2 ? 0 : plane + 1, b_axis = plane == 0 ? 2 : plane - 1;
+    float t = (B.x - comp(o, k_axis)) / comp(d, k_axis);
+    if (t < t_min || t > t_max) return false;
+    float x = fmaf(t, comp(d, a_axis), comp(o, a_axis));
+    float y = fmaf(t, comp(d, b_axis), comp(o, b_axis));
+    if (x < A.x || x > A.z || y < A.y || y > A.w) return false;
+    *t_out = t;
+    return true;
+  }
+  // DP_BOX
+  float ix = 1.0f / d.x, iy = 1.0f / d.y, iz = 1.0f / d.z;
+  float tx0 = (A.x - o.x) * ix, tx1 = (B.x - o.x) * ix;
+  float ty0 = (A.y - o.y) * iy, ty1 = (B.y - o.y) * iy;
+  float tz0 = (A.z - o.z) * iz, tz1 = (B.z - o.z) * iz;
+  float nx = fminf(tx0, tx1), fx = fmaxf(tx0, tx1);
+  float ny = fminf(ty0, ty1), fy = fmaxf(ty0, ty1);
+  float nz = fminf(tz0, tz1), fz = fmaxf(tz0, tz1);
+  if (self) {
+    // origin lies on face `self_face` (axis 2 - face/2; odd = min plane)
+    const int ax = 2 - (self_face >> 1);
+    const bool is_min = self_face & 1;
+    const float dk = comp(d, ax);
+    const bool entering = is_min ? dk > 0.0f : dk < 0.0f;  // that plane is the near plane of its slab
+    const float nn = entering ? -CUDART_INF_F : (ax == 0 ? nx : (ax == 1 ? ny : nz));
+    const float ff = entering ? (ax == 0 ? fx : (ax == 1 ? fy : fz)) : 0.0f;
+    if (ax == 0) nx = nn, fx = ff;
+    else if (ax == 1) ny = nn, fy = ff;
+    else nz = nn, fz = ff;
+  }
+  float t_enter = fmaxf(fmaxf(nx, ny), nz);
+  float t_exit = fminf(fminf(fx, fy), fz);
+  if (!(t_enter <= t_exit)) return false;
+  // candidates in list-scan terms: the entry face, then the exit face
+  if (t_enter >= t_min && t_enter <= t_max) {
+    int ax = (nx >= ny && nx >= nz) ? 0 : (ny >= nz ? 1 : 2);
+    float dk = comp(d, ax);
+    *t_out = t_enter;
+    *face_out = ((2 - ax) << 1) | (dk > 0.0f ? 1 : 0);  // entering through the min plane when d > 0
+    return true;
+  }
+  if (t_exit >= t_min && t_exit <= t_max) {
+    int ax = (fx <= fy && fx <= fz) ? 0 : (fy <= fz ? 1 : 2);
+    float dk = comp(d, ax);
+    *t_out = t_exit;
+    *face_out = ((2 - ax) << 1) | (dk > 0.0f ? 0 : 1);  // leaving through the max plane when d > 0
+    return true;
+  }
+  return false;
+}
+
+#define RTB_STACK_DEPTH 64
+
+// Closest surface hit over (t_min, +inf): the result of world.hit(ray, 0.001, f64::MAX)
+// (src/color.rs:7) restricted to surfaces.  Stack-based traversal of the two-child BVH,
+// near child first, far child pushed, the query interval shrinking with every accepted hit.
+template <bool kStats>
+__device__ __forceinline__ Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int self_prim,
+                                             int self_face, Counters* cnt) {
+  Hit best;
+  best.t = CUDART_INF_F, best.prim = -1, best.face = 0;
+  const float inv_a = 1.0f / dot(ray.d, ray.d);
+  auto safe_inv = [](float v) { return 1.0f / (fabsf(v) > 1e-20f ? v : copysignf(1e-20f, v)); };
+  const float idx = safe_inv(ray.d.x), idy = safe_inv(ray.d.y), idz = safe_inv(ray.d.z);
+  const float oodx = ray.o.x * idx, oody = ray.o.y * idy, oodz = ray.o.z * idz;
+
+  int stack[RTB_STACK_DEPTH];
+  int sp = 0;
+  int cur = sv.root;
+  for (;;) {
+    while (cur >= 0) {
+      if (kStats) cnt->node_tests++;
+      const DNode* nd = sv.nodes + cur;
+      const float4 n0 = ldg4(&nd->n0), n1 = ldg4(&nd->n1), n2 = ldg4(&nd->n2);
+      const int4 n3 = ldg4i(&nd->n3);
+      float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
+      float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
+      float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
+      float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
+      float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
+      float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
+      float tn0 = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
+      float tf0 = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
+      float tn1 = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
+      float tf1 = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
+      const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+      if (h0 && h1) {
+        int near = n3.x, far = n3.y;
+        if (tn1 < tn0) near = n3.y, far = n3.x;
+        stack[sp++] = far;
+        cur = near;
+      } else if (h0) {
+        cur = n3.x;
+      } else if (h1) {
+        cur = n3.y;
+      } else {
+        if (sp == 0) return best;
+        cur = stack[--sp];
+      }
+    }
+    // leaf
+    const unsigned code = ~(unsigned)cur;
+    const int first = (int)(code >> 3), count = (int)(code & 7u);
+    for (int i = 0; i < count; ++i) {
+      const int pi = first + i;
+      float t;
+      int face = 0;
+      if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, t_min, best.t, pi == self_prim, self_face, &t,
+                                 &face, cnt)) {
+        best.t = t, best.prim = pi, best.face = face;
+      }
+    }
+    if (sp == 0) return best;
+    cur = stack[--sp];
+  }
+}
+
+// ---- surface point ------------------------------------------------------------------------------
+struct Surface {
+  V3f p, n;  // world-space hit point and shading normal (FlipNormals applied)
+  float u, v;
+  int mat;
+  int prim_id;
+};
+
+__device__ __forceinline__ void sphere_uv(V3f n, float* u, float* v) {  // src/sphere.rs:9-15 (Q5: FRAC_2_PI)
+  float phi = atan2f(n.z, n.x);
+  float theta = asinf(fminf(1.0f, fmaxf(-1.0f, n.y)));
+  *u = 1.0f - (phi + CUDART_PI_F) * (0.5f / CUDART_PI_F);
+  *v = (theta + 0.63661977236758134308f) * (1.0f / CUDART_PI_F);
+}
+
+// Fills the HitRecord fields (src/hittable.rs:9-16) of an accepted hit.  u,v are only computed
+// when the material's texture chain can read them (ImageTexture); the reference computes
+// atan2/asin on every sphere hit (src/sphere.rs:50,64).
+__device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim* __restrict__ prims, const RayF& ray,
+                                                const Hit& h) {
+  Surface s;
+  const float4 A = ldg4(&prims[h.prim].a);
+  const float4 B = ldg4(&prims[h.prim].b);
+  const int4 C = ldg4i(&prims[h.prim].c);
+  const int type = RTB_PRIM_TYPE(C.x);
+  const int xi = RTB_PRIM_XFORM(C.x);
+  s.mat = C.y;
+  s.prim_id = C.z;
+  s.u = 0.0f, s.v = 0.0f;
+  const bool need_uv = __ldg(&sv.mats[C.y].needs_uv) != 0;
+  if (type <= DP_MOVING_SPHERE) {
+    V3f ctr = sphere_center(A, B, C, ray.time);
+    s.p = madd(h.t, ray.d, ray.o);
+    float inv_r = 1.0f / A.w;
+    s.n = inv_r * (s.p - ctr);
+    if (need_uv) {
+      V3f nl = s.n;
+      if (xi != 0) nl = xf_vec(load_xform(sv.xforms, xi), s.n);  // uv is taken in the sphere's own frame
+      sphere_uv(nl, &s.u, &s.v);
+    }
+  } else {
+    V3f o = ray.o, d = ray.d;
+    DXform x;
+    if (xi != 0) {
+      x = load_xform(sv.xforms, xi);
+      o = xf_point(x, ray.o);
+      d = xf_vec(x, ray.d);
+    }
+    V3f pl = madd(h.t, d, o);
+    int k_axis;
+    float a0, b0, a1, b1;  // the face's (x0,y0,x1,y1) in its (a,b) axes
+    if (type == DP_RECT) {
+      k_axis = RTB_PRIM_PLANE(C.x);
+      set_comp(pl, k_axis, B.x);  // the hit point lies on the plane exactly
+      a0 = A.x, b0 = A.y, a1 = A.z, b1 = A.w;
+    } else {
+      k_axis = 2 - (h.face >> 1);
+      const bool is_min = h.face & 1;
+      set_comp(pl, k_axis, is_min ? comp(mk(A.x, A.y, A.z), k_axis) : comp(mk(B.x, B.y, B.z), k_axis));
+      s.prim_id += h.face;
+      const int aa = k_axis == 2 ? 0 : k_axis + 1, bb = k_axis == 0 ? 2 : k_axis - 1;
+      a0 = comp(mk(A.x, A.y, A.z), aa), b0 = comp(mk(A.x, A.y, A.z), bb);
+      a1 = comp(mk(B.x, B.y, B.z), aa), b1 = comp(mk(B.x, B.y, B.z), bb);
+    }
+    if (need_uv) {
+      const int aa = k_axis == 2 ? 0 : k_axis + 1, bb = k_axis == 0 ? 2 : k_axis - 1;
+      s.u = (comp(pl, aa) - a0) / (a1 - a0);  // src/rect.rs:54-55
+      s.v = (comp(pl, bb) - b0) / (b1 - b0);
+    }
+    V3f nl = mk(k_axis == 0 ? 1.0f : 0.0f, k_axis == 1 ? 1.0f : 0.0f, k_axis == 2 ? 1.0f : 0.0f);  // always +e_k (Q9)
+    if (xi != 0) {
+      s.p = xf_point_inv(x, pl);
+      s.n = xf_vec_t(x, nl);
+    } else {
+      s.p = pl;
+      s.n = nl;
+    }
+  }
+  if (RTB_PRIM_FLIP(C.x)) s.n = -s.n;
+  return s;
+}
+
+// ---- constant media: src/medium.rs:28-56 -------------------------------------------------------
+// boundary.hit(ray, lo, +inf) over the medium's boundary primitives, list order, closest wins.
+template <bool kStats>
+__device__ __forceinline__ bool boundary_hit(const SceneView& sv, const DMedium& m, const RayF& ray, float inv_a, float lo,
+                                             float* t_out, Counters* cnt) {
+  float best = CUDART_INF_F;
+  bool any = false;
+  for (int i = 0; i < m.count; ++i) {
+    float t;
+    int face;
+    if (intersect_prim<kStats>(sv.bprims, m.first + i, sv.xforms, ray, inv_a, lo, best, false, 0, &t, &face, cnt)) {
+      best = t;
+      any = true;
+    }
+  }
+  *t_out = best;
+  return any;
+}
+
+// Runs every medium against the ray after the surface query.  Per medium (reference order):
+// hit1 = boundary.hit(-MAX, MAX); hit2 = boundary.hit(hit1.t + 1e-4, MAX); clamp to
+// [t_min, closest_so_far]; exponential free flight.  Independent exponentials clipped to the
+// running closest hit give the same distribution as the reference's list scan (Q13).
+// Returns the index of the medium that scattered, or -1.
+template <bool kStats>
+__device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray, float t_min, float* t_closest,
+                                            PathRng& rng, Counters* cnt) {
+  int which = -1;
+  const float a = dot(ray.d, ray.d);
+  const float inv_a = 1.0f / a;
+  const float len = sqrtf(a);
+  for (int mi = 0; mi < sv.n_media; ++mi) {
+    if (kStats) cnt->medium_tests++;
+    DMedium m;
+    {
+      int4 raw = __ldg(reinterpret_cast<const int4*>(sv.media + mi));
+      m.first = raw.x, m.count = raw.y, m.mat = raw.z, m.neg_inv_density = __int_as_float(raw.w);
+    }
+    float t1, t2;
+    if (!boundary_hit<kStats>(sv, m, ray, inv_a, -CUDART_INF_F, &t1, cnt)) continue;
+    if (!boundary_hit<kStats>(sv, m, ray, inv_a, t1 + 0.0001f, &t2, cnt)) continue;
+    if (t1 < t_min) t1 = t_min;
+    if (t2 > *t_closest) t2 = *t_closest;
+    if (t1 < t2) {
+      float distance_inside = (t2 - t1) * len;
+      float hit_distance = m.neg_inv_density * __logf(rng.next());
+      if (hit_distance < distance_inside) {
+        *t_closest = t1 + hit_distance / len;
+        which = mi;
+      }
+    }
+  }
+  return which;
+}
+
+// ---- textures: src/texture.rs, src/perlin.rs --------------------------------------------------
+__device__ __forceinline__ float perlin_noise(const DPerlin* __restrict__ P, V3f p) {  // src/perlin.rs:76-97
+  float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
+  float u = p.x - fx, v = p.y - fy, w = p.z - fz;
+  // `floor(x) as usize`: negatives (and NaN) saturate to 0 (Q18); large values wrap with & 255
+  // exactly like the usize arithmetic as long as they fit 2^31, which scene coordinates do
+  int i = fx > 0.0f ? (int)fminf(fx, 2147483520.0f) : 0;
+  int j = fy > 0.0f ? (int)fminf(fy, 2147483520.0f) : 0;
+  int k = fz > 0.0f ? (int)fminf(fz, 2147483520.0f) : 0;
+  float uu = u * u * (3.0f - 2.0f * u);
+  float vv = v * v * (3.0f - 2.0f * v);
+  float ww = w * w * (3.0f - 2.0f * w);
+  unsigned px0 = __ldg(&P->perm_x[i & 255]), px1 = __ldg(&P->perm_x[(i + 1) & 255]);
+  unsigned py0 = __ldg(&P->perm_y[j & 255]), py1 = __ldg(&P->perm_y[(j + 1) & 255]);
+  unsigned pz0 = __ldg(&P->perm_z[k & 255]), pz1 = __ldg(&P->perm_z[(k + 1) & 255]);
+  float accum = 0.0f;
+#pragma unroll
+  for (int di = 0; di < 2; ++di)
+#pragma unroll
+    for (int dj = 0; dj < 2; ++dj)
+#pragma unroll
+      for (int dk = 0; dk < 2; ++dk) {
+        unsigned idx = (di ? px1 : px0) ^ (dj ? py1 : py0) ^ (dk ? pz1 : pz0);
+        float4 c = ldg4(&P->ranvec[idx]);
+        float wgt = (di ? uu : 1.0f - uu) * (dj ? vv : 1.0f - vv) * (dk ? ww : 1.0f - ww);
+        accum = fmaf(wgt, fmaf(c.x, u - (float)di, fmaf(c.y, v - (float)dj, c.z * (w - (float)dk))), accum);
+      }
+  return accum;
+}
+
+__device__ __forceinline__ float perlin_turb(const DPerlin* __restrict__ P, V3f p) {  // src/perlin.rs:99-109, depth 7
+  float accum = 0.0f, weight = 1.0f;
+#pragma unroll 1
+  for (int d = 0; d < 7; ++d) {
+    accum = fmaf(weight, perlin_noise(P, p), accum);
+    weight *= 0.5f;
+    p = 2.0f * p;
+  }
+  return fabsf(accum);
+}
+
+struct TexCounters {
+  unsigned long long n[4];
+};
+
+template <bool kStats>
+__device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p, TexCounters* tc) {
+  for (;;) {
+    const int4 hd = __ldg(reinterpret_cast<const int4*>(sv.texs + tex));
+    const int type = hd.x;
+    if (kStats) tc->n[type & 3]++;
+    if (type == RTB_TEX_CHECKER) {  // src/texture.rs:40-47: product of three sines < 0 -> `odd`
+      float s = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
+      tex = s < 0.0f ? hd.y : hd.z;
+      continue;
+    }
+    const float4 col = __ldg(reinterpret_cast<const float4*>(sv.texs + tex) + 1);
+    if (type == RTB_TEX_SOLID) return mk(col.x, col.y, col.z);
+    if (type == RTB_TEX_NOISE) {  // src/texture.rs:66-70
+      float t = perlin_turb(sv.perlin + hd.y, p);
+      float g = 0.5f * (1.0f + sinf(fmaf(col.w, p.x, 5.0f * t)));
+      return mk(g, g, g);
+    }
+    // RTB_TEX_IMAGE, src/texture.rs:87-107: saturating casts, clamp high, nearest texel
+    const int nx = hd.y, ny = hd.z;
+    float fi = u * (float)nx, fj = (1.0f - v) * (float)ny;
+    int i = fi > 0.0f ? (int)fminf(fi, 2147483520.0f) : 0;
+    int j = fj > 0.0f ? (int)fminf(fj, 2147483520.0f) : 0;
+    if (i > nx - 1) i = nx - 1;
+    if (j > ny - 1) j = ny - 1;
+    uint32_t texel = __ldg(&sv.texels[hd.w + i + nx * j]);
+    const float k = 1.0f / 255.0f;
+    return mk((float)(texel & 255u) * k, (float)((texel >> 8) & 255u) * k, (float)((texel >> 16) & 255u) * k);
+  }
+}
+
+// ---- materials: src/material.rs ------------------------------------------------------------------
+__device__ __forceinline__ V3f reflect(V3f v, V3f n) { return v - (2.0f * dot(v, n)) * n; }  // :9-11
+
+// Material::scatter.  Returns false when the path ends (DiffuseLight, absorbed Metal).
+// On success `ray` becomes the scattered ray (origin = hit.p, same time) and *atten the albedo.
+template <bool kStats>
+__device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int mat_tex, float mat_param, const Surface& s,
+                                        RayF& ray, PathRng& rng, V3f* atten, TexCounters* tc) {
+  switch (mat_type) {
+    case RTB_MAT_LAMBERTIAN: {  // :49-53  target - p = normal + ball
+      V3f dir = s.n + sample_unit_ball(rng);
+      *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
+      ray.o = s.p, ray.d = dir;
+      return true;
+    }
+    case RTB_MAT_METAL: {  // :76-86
+      float inv_len = rsqrtf(dot(ray.d, ray.d));
+      V3f reflected = reflect(inv_len * ray.d, s.n);
+      if (mat_param > 0.0f) reflected = madd(mat_param, sample_unit_ball(rng), reflected);
+      if (dot(reflected, s.n) > 0.0f) {
+        *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
+        ray.o = s.p, ray.d = reflected;
+        return true;
+      }
+      return false;
+    }
+    case RTB_MAT_DIELECTRIC: {  // :106-126
+      *atten = mk(1.0f, 1.0f, 1.0f);
+      const float ref_idx = mat_param;
+      const float ddn = dot(ray.d, s.n);
+      const float inv_len = rsqrtf(dot(ray.d, ray.d));
+      V3f outward_normal;
+      float ni_over_nt, cosine;
+      if (ddn > 0.0f) {
+        cosine = ref_idx * ddn * inv_len;
+        outward_normal = -s.n;
+        ni_over_nt = ref_idx;
+      } else {
+        cosine = -ddn * inv_len;
+        outward_normal = s.n;
+        ni_over_nt = 1.0f / ref_idx;
+      }
+      // refract(), :13-23
+      V3f uv = inv_len * ray.d;
+      float dt = dot(uv, outward_normal);
+      float discriminant = 1.0f - ni_over_nt * ni_over_nt * (1.0f - dt * dt);
+      if (discriminant > 0.0f) {
+        float r0 = (1.0f - ref_idx) / (1.0f + ref_idx);  // schlick(), :25-28
+        r0 = r0 * r0;
+        float m = 1.0f - cosine;
+        float m2 = m * m;
+        float reflect_prob = r0 + (1.0f - r0) * (m2 * m2 * m);
+        if (rng.next() >= reflect_prob) {
+          V3f refracted = ni_over_nt * (uv - dt * outward_normal) - sqrtf(discriminant) * outward_normal;
+          ray.o = s.p, ray.d = refracted;
+          return true;
+        }
+      }
+      V3f reflected = reflect(ray.d, s.n);  // un-normalised d, unflipped hit.normal (Q14)
+      ray.o = s.p, ray.d = reflected;
+      return true;
+    }
+    case RTB_MAT_ISOTROPIC: {  // :165-168
+      *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
+      ray.o = s.p, ray.d = sample_unit_ball(rng);
+      return true;
+    }
+    default:  // RTB_MAT_DIFFUSE_LIGHT :144-146
+      return false;
+  }
+}
+
+// ---- camera: src/camera.rs:53-67 ------------------------------------------------------------------
+// Draws (in stream order): jitter_u, jitter_v, lens_r, lens_phi, time.  The lens sample is the
+// uniform unit disk (r = sqrt(xi), phi = 2 pi xi) — same distribution as the rejection loop at
+// src/util.rs:15-24.  The lens draws are consumed even when lens_radius == 0 so the stream
+// layout is fixed; the time draw always happens, as upstream.
+__device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, PathRng& rng) {
+  float ju = rng.next(), jv = rng.next(), lr = rng.next(), lp = rng.next(), xt = rng.next();
+  float s = ((float)i + ju) / (float)nx;  // tests/test.rs:66-67
+  float t = ((float)j + jv) / (float)ny;
+  V3f origin = mk(cam.origin[0], cam.origin[1], cam.origin[2]);
+  if (cam.lens_radius != 0.0f) {
+    float r = cam.lens_radius * sqrtf(lr);
+    float sn, cs;
+    __sincosf((2.0f * lp - 1.0f) * CUDART_PI_F, &sn, &cs);
+    float rx = r * cs, ry = r * sn;
+    origin = mk(fmaf(cam.u[0], rx, fmaf(cam.v[0], ry, origin.x)), fmaf(cam.u[1], rx, fmaf(cam.v[1], ry, origin.y)),
+                fmaf(cam.u[2], rx, fmaf(cam.v[2], ry, origin.z)));
+  }
+  RayF ray;
+  ray.o = origin;
+  ray.d = mk(cam.llc[0] + s * cam.horizontal[0] + t * cam.vertical[0] - origin.x,
+             cam.llc[1] + s * cam.horizontal[1] + t * cam.vertical[1] - origin.y,
+             cam.llc[2] + s * cam.horizontal[2] + t * cam.vertical[2] - origin.z);
+  ray.time = cam.time0 + xt * (cam.time1 - cam.time0);
+  return ray;
+}
+
+__device__ __forceinline__ V3f background_color(int background, V3f d) {
+  if (background == 1) {  // the gradient commented out at src/color.rs:18-20 (lit variant only)
+    float inv = rsqrtf(dot(d, d));
+    float t = 0.5f * (d.y * inv + 1.0f);
+    return mk((1.0f - t) + t * 0.5f, (1.0f - t) + t * 0.7f, (1.0f - t) + t * 1.0f);
+  }
+  return mk(0.0f, 0.0f, 0.0f);  // src/color.rs:21
+}
+
+}  // namespace rtb
