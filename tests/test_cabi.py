@@ -1,0 +1,127 @@
+"""C-ABI boundary: the library loads without a GPU, exports every symbol include/rtb200.h
+declares, and mirrors the reference's error behaviour (None / panic -> error codes).  No compute
+calls here."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def declared_symbols():
+    text = (ROOT / "include" / "rtb200.h").read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(rtb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_every_declared_symbol_is_exported(rtb):
+    syms = declared_symbols()
+    assert len(syms) >= 35
+    missing = [s for s in syms if not hasattr(rtb.lib, s)]
+    assert not missing, missing
+
+
+def test_header_compiles_as_c(tmp_path):
+    import subprocess
+    src = tmp_path / "t.c"
+    src.write_text('#include "rtb200.h"\nint main(void){ rtb_render_opts o; (void)o; return sizeof(RtbObjRec) == 112 ? 0 : 1; }\n')
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", str(ROOT / "include"), "-c", str(src), "-o",
+                    str(tmp_path / "t.o")], check=True)
+
+
+def test_struct_layouts_match_ctypes(rtb):
+    # sizes the Python mirror assumes (include/rtb200.h, rtb_scene_format.h)
+    assert C.sizeof(rtb.RtbCamera) == 15 * 8
+    assert C.sizeof(rtb.RenderOpts) == 80
+    assert C.sizeof(rtb.Stats) == (5 + 5 + 4 + 1) * 8 + 8 + 8 * 8
+    o = rtb.default_opts()
+    assert (o.max_depth, o.t_min, o.background, o.sample_stride) == (50, 1e-3, 0, 1)  # src/color.rs:7,9
+
+
+def test_bad_handles_are_errors_not_crashes(rtb):
+    s = rtb.Scene()
+    with pytest.raises(rtb.RtbError):
+        s.lambertian(3)  # no such texture
+    t = s.solid(0.5, 0.5, 0.5)
+    with pytest.raises(rtb.RtbError):
+        s.sphere((0, 0, 0), 1.0, 7)  # no such material
+    m = s.lambertian(t)
+    with pytest.raises(rtb.RtbError):
+        s.flip_normals(0)  # no objects yet
+    sp = s.sphere((0, 0, 0), 1.0, m)
+    with pytest.raises(rtb.RtbError):
+        s.list([sp, 99])
+    with pytest.raises(rtb.RtbError):
+        s.rect(5, 0, 0, 1, 1, 0, m)  # bad plane
+
+
+def test_empty_bvh_is_the_reference_panic(rtb):
+    # BVHNode::new on an empty slice panics (src/bvh.rs:43-51) -> RTB_ERR_NO_BBOX
+    s = rtb.Scene()
+    with pytest.raises(rtb.RtbError) as e:
+        s.bvh([])
+    assert e.value.code == -4
+
+
+def test_serialize_roundtrip_is_identical(rtb):
+    for name in ("cornell_smoke", "two_perlin_sphere", "random_scene"):
+        s, w, _ = rtb.Scene.named(name, 32, 18)
+        b = s.serialize()
+        s2 = rtb.Scene.deserialize(b)
+        assert s2.serialize() == b
+        assert s2.prim_count(w) == s.prim_count(w)
+    with pytest.raises(rtb.RtbError):
+        rtb.Scene.deserialize(b[:100])
+    bad = bytearray(b)
+    bad[0] ^= 0xFF
+    with pytest.raises(rtb.RtbError):
+        rtb.Scene.deserialize(bytes(bad))
+
+
+def test_named_scene_inventory(rtb):
+    # primitive totals of tests/test.rs:89-523
+    expect = {"two_spheres": 2, "two_perlin_sphere": 2, "earth": 1, "simple_light": 4, "cornell_box": 6 + 12,
+              "cornell_smoke": 6 + 12, "final_scene": 2400 + 1 + 5 + 2 + 1 + 1000}
+    for name, n in expect.items():
+        s, w, cam = rtb.Scene.named(name, 64, 64)
+        assert s.prim_count(w) == n, name
+    s, w, cam = rtb.Scene.named("random_scene", 1280, 720)
+    n = s.prim_count(w)
+    assert 380 <= n <= 404  # 400 grid cells minus those near (4,0.2,0), plus ground + 3 (F10)
+    assert abs(cam.aspect - 1280 / 720) < 1e-15 and cam.vertical_fov == 20.0 and cam.aperture == 0.1
+    with pytest.raises(rtb.RtbError):
+        rtb.Scene.named("no_such_scene", 8, 8)
+    # seeds are reproducible and distinct
+    a = rtb.Scene.named("random_scene", 8, 8, seed=7)[0].serialize()
+    b = rtb.Scene.named("random_scene", 8, 8, seed=7)[0].serialize()
+    c = rtb.Scene.named("random_scene", 8, 8, seed=8)[0].serialize()
+    assert a == b and a != c
+
+
+def test_ppm_p3_text_matches_reference_format(rtb):
+    # tests/test.rs:59 header and :79 "{} {} {}\n" per pixel
+    img = np.array([[[0, 1, 2], [10, 99, 100]], [[255, 254, 7], [0, 0, 0]]], np.uint8)
+    assert rtb.ppm_p3(img) == b"P3\n2 2\n255\n0 1 2\n10 99 100\n255 254 7\n0 0 0\n"
+
+
+def test_no_device_is_a_loud_error(rtb):
+    if rtb.device_count() > 0:
+        pytest.skip("a GPU is present")
+    s, w, cam = rtb.Scene.named("two_spheres", 8, 8)
+    with pytest.raises(rtb.RtbError) as e:
+        s.render(w, cam, 8, 8, 1)
+    assert e.value.code == -2  # RTB_ERR_NO_DEVICE: no CPU fallback
+
+
+def test_primary_rays_are_deterministic_and_in_frustum(rtb):
+    _, _, cam = rtb.Scene.named("cornell_box", 16, 16)
+    a = rtb.primary_rays(cam, 16, 16, sample=3, seed=11)
+    b = rtb.primary_rays(cam, 16, 16, sample=3, seed=11)
+    c = rtb.primary_rays(cam, 16, 16, sample=4, seed=11)
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    assert np.all((a[:, 6] >= 0) & (a[:, 6] < 1))  # time in [t0, t1)  (src/camera.rs:61)
+    # lens offsets stay inside aperture/2 of the eye (src/camera.rs:57-59)
+    assert np.all(np.linalg.norm(a[:, :3] - np.array([278, 278, -800.0]), axis=1) <= 0.05 + 1e-12)

@@ -1,0 +1,210 @@
+"""GPU parity tests proper (run on the B200 box with -m gpu).  Everything goes through the C ABI
+(librtb200.so) and is checked against the CPU oracle on the same serialized scene bytes."""
+import hashlib
+import json
+import os
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from parity_utils import image_parity
+
+pytestmark = pytest.mark.gpu
+GOLD = json.loads((Path(__file__).parent / "golden" / "kat_ppm.json").read_text())
+NT = os.cpu_count() or 1
+ALL_SCENES = ("random_scene", "two_spheres", "two_perlin_sphere", "earth", "simple_light", "cornell_box",
+              "cornell_smoke", "final_scene", "final_scene_lit", "cornell_smoke_book")
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _need_gpu(rtb):
+    assert rtb.device_count() > 0, "GPU tests need a CUDA device; the product has no CPU fallback"
+
+
+# ---- 1. closest-hit primitive IDs: >= 99.99 % of >= 2^20 primary rays (north_star) ----------------
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_closest_hit_ids_agree_with_oracle(rtb, orc, name):
+    nx = ny = 1024  # 2^20 primary rays: jittered, with lens and time samples (fixed seed)
+    s, w, cam = rtb.Scene.named(name, nx, ny)
+    rays = rtb.primary_rays(cam, nx, ny, sample=0, seed=20240607)
+    o = orc.OracleScene(s.serialize(), w)
+    p_ref, t_ref = o.closest_hit(rays, media=False)
+    p_gpu, t_gpu = s.closest_hit(w, rays)
+    agree = float((p_ref == p_gpu).mean())
+    assert agree >= 0.9999, f"{name}: {agree:.6f}"
+    both = (p_ref == p_gpu) & (p_ref >= 0)
+    if both.any():
+        rel = np.abs(t_gpu[both] - t_ref[both]) / np.maximum(np.abs(t_ref[both]), 1e-3)
+        assert np.quantile(rel, 0.999) < 2e-4, f"{name}: t rel err q99.9 = {np.quantile(rel, 0.999):.2e}"
+    if name in ("two_spheres", "two_perlin_sphere", "earth", "simple_light"):
+        assert (p_ref >= 0).mean() > 0.05  # the batch is not vacuous
+
+
+def test_closest_hit_secondary_rays_inside_geometry(rtb, orc):
+    # rays that start inside the cornell box / between the final_scene objects, random directions
+    rng = np.random.default_rng(5)
+    for name, lo, hi in (("cornell_box", (1, 1, 1), (554, 554, 554)), ("final_scene", (-900, 120, -900), (900, 500, 900)),
+                         ("random_scene", (-10, 0.5, -10), (10, 3, 10))):
+        s, w, cam = rtb.Scene.named(name, 8, 8)
+        n = 200_000
+        rays = np.zeros((n, 7))
+        rays[:, :3] = rng.uniform(lo, hi, (n, 3))
+        rays[:, 3:6] = rng.normal(size=(n, 3))
+        rays[:, 6] = rng.uniform(0, 1, n)
+        o = orc.OracleScene(s.serialize(), w)
+        p_ref, t_ref = o.closest_hit(rays, media=False)
+        p_gpu, t_gpu = s.closest_hit(w, rays)
+        agree = float((p_ref == p_gpu).mean())
+        assert agree >= 0.9999, f"{name}: {agree:.6f}"
+
+
+# ---- 2. textures --------------------------------------------------------------------------------------
+def test_texture_values_match_oracle(rtb, orc):
+    rng = np.random.default_rng(2)
+    s = rtb.Scene()
+    t_noise = s.noise(4.0, seed=77)
+    t_noise2 = s.noise(0.1, seed=78)
+    t_check = s.checker(s.solid(0.2, 0.3, 0.1), s.solid(0.9, 0.9, 0.9))
+    t_nested = s.checker(t_check, t_noise)
+    t_img = s.image(rtb.earth_rgb8())
+    w = s.sphere((0, 0, 0), 1.0, s.lambertian(t_nested))
+    o = orc.OracleScene(s.serialize(), w)
+    n = 100_000
+    uvp = np.concatenate([rng.uniform(-0.4, 1.2, (n, 2)), rng.uniform(-30, 30, (n, 3))], axis=1)
+    uvp[: n // 4, 2:] *= 30.0  # far from the origin too (|p| up to 900)
+    for tex, tol, frac in ((t_noise, 3e-3, 0.998), (t_noise2, 3e-3, 0.998), (t_check, 1e-6, 0.998),
+                           (t_nested, 3e-3, 0.995), (t_img, 1e-6, 0.999)):
+        a = o.texture_value(tex, uvp)
+        b = s.texture_value(w, tex, uvp)
+        ok = np.abs(a - b).max(axis=1) <= tol
+        assert ok.mean() >= frac, (tex, ok.mean(), np.abs(a - b).max())
+
+
+# ---- 3. the reference's own known-answer vectors, on the GPU ------------------------------------------
+@pytest.mark.parametrize("fname", sorted(GOLD))
+def test_kat_committed_renders_reproduced_byte_for_byte(rtb, fname):
+    g = GOLD[fname]
+    s, w, cam = rtb.Scene.named(g["scene"], g["nx"], g["ny"])
+    ppm = rtb.create_image(g["ny"], g["nx"], g["ns"], cam, s, w)  # (ny, nx, ns, cam, world), tests/test.rs:55
+    assert len(ppm) == g["bytes"]
+    assert hashlib.sha256(ppm).hexdigest() == g["sha256"]
+    _, _, st = s.render(w, cam, 200, 200, 8, rtb.default_opts(collect_stats=1), want_stats=True)
+    assert st["segments"] > 1.5 * st["paths"]  # black because light is unreachable, not because nothing ran
+
+
+# ---- 4. images: noise-floor-relative PSNR against the oracle ---------------------------------------------
+IMAGE_CASES = [
+    # name, background, nx, ny, spp
+    ("two_spheres", 1, 200, 112, 256),
+    ("random_scene", 1, 160, 90, 128),
+    ("two_perlin_sphere", 1, 160, 90, 128),
+    ("earth", 1, 160, 90, 128),
+    ("simple_light", 0, 96, 54, 512),
+    ("cornell_box", 0, 64, 64, 2048),
+    ("cornell_smoke_book", 0, 64, 64, 1024),
+    ("final_scene_lit", 0, 64, 64, 512),
+]
+
+
+@pytest.mark.parametrize("name,bg,nx,ny,ns", IMAGE_CASES)
+def test_image_matches_oracle_within_noise_floor(rtb, orc, name, bg, nx, ny, ns):
+    s, w, cam = rtb.Scene.named(name, nx, ny)
+    o = orc.OracleScene(s.serialize(), w)
+    a, _, _ = o.render(cam, nx, ny, ns, background=bg, seed=101, nthreads=NT)
+    b, _, _ = o.render(cam, nx, ny, ns, background=bg, seed=202, nthreads=NT)
+    g_sum, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=7), want_rgb8=False)
+    hi = 16 * ns
+    h_sum, _, _ = s.render(w, cam, nx, ny, hi, rtb.default_opts(background=bg, seed=9), want_rgb8=False)
+    r = image_parity(g_sum / ns, h_sum / hi, a, b)
+    print(name, {k: (round(v, 2) if isinstance(v, float) else [round(x, 4) for x in v]) for k, v in r.items()})
+    assert r["gpu_db"] >= r["floor_db"] - 0.5, r          # as good as a second oracle run
+    assert r["bias_db"] >= r["floor_db"] + 4.0, r         # and unbiased: ~ +6 dB when GPU noise vanishes
+    if r["floor_db"] >= 40.5:
+        assert r["gpu_db"] >= 40.0, r                      # >= 40 dB where the floor permits (north_star)
+    for c in range(3):
+        assert abs(r["mean_ratio"][c] - 1.0) < 0.02, r
+
+
+def test_high_spp_image_reaches_40db(rtb, orc):
+    # one case where the floor itself clears 40 dB: C1's scene, sky-lit variant
+    nx, ny, ns = 100, 56, 2048
+    s, w, cam = rtb.Scene.named("two_spheres", nx, ny)
+    o = orc.OracleScene(s.serialize(), w)
+    a, _, _ = o.render(cam, nx, ny, ns, background=1, seed=5, nthreads=NT)
+    g_sum, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=1, seed=3), want_rgb8=False)
+    from parity_utils import gamma01, psnr
+    db = psnr(gamma01(g_sum / ns), gamma01(a))
+    assert db >= 40.0, db
+
+
+# ---- 5. analytic scenes on the GPU -------------------------------------------------------------------
+def test_furnace_gpu(rtb):
+    s = rtb.Scene()
+    lam = s.lambertian(s.solid(0.25, 0.5, 0.75))
+    light = s.diffuse_light(s.solid(1, 1, 1))
+    w = s.list([s.sphere((0, 0, 0), 1.0, lam), s.sphere((0, 0, 0), 100.0, light)])
+    cam = rtb.camera((0, 0, 5), (0, 0, 0), (0, 1, 0), 10.0, 1.0, 0.0, 5.0, 0.0, 1.0)
+    g, rgb8, st = s.render(w, cam, 16, 16, 64, rtb.default_opts(collect_stats=1), want_stats=True)
+    np.testing.assert_allclose(g.reshape(-1, 3) / 64, np.tile([0.25, 0.5, 0.75], (256, 1)), rtol=2e-6)
+    assert st["segments"] == 2 * st["paths"] == 2 * 16 * 16 * 64
+    assert st["shade"][0] == st["paths"] and st["shade"][3] == st["paths"]  # one Lambertian, one light hit
+    # quantisation: int(255.99*sqrt(c))  (tests/test.rs:73-78)
+    np.testing.assert_array_equal(rgb8[0, 0], [int(255.99 * np.sqrt(c)) for c in (0.25, 0.5, 0.75)])
+
+
+def test_beer_lambert_gpu(rtb):
+    density, thickness = 0.05, 20.0
+    s = rtb.Scene()
+    light = s.diffuse_light(s.solid(1, 1, 1))
+    box = s.cube((-50, -50, 0), (50, 50, thickness), s.lambertian(s.solid(0, 0, 0)))
+    med = s.constant_medium(box, density, s.solid(0, 0, 0))
+    w = s.list([med, s.rect(rtb.PLANE_XY, -500, -500, 500, 500, thickness + 5.0, light)])
+    cam = rtb.camera((0, 0, -100), (0, 0, 0), (0, 1, 0), 0.5, 1.0, 0.0, 100.0, 0.0, 1.0)
+    nx = ny = 64
+    ns = 256
+    g, _, _ = s.render(w, cam, nx, ny, ns, want_rgb8=False)
+    p = np.exp(-density * thickness)
+    sigma = np.sqrt(p * (1 - p) / (nx * ny * ns))
+    assert abs(g[..., 0].mean() / ns - p) < 5 * sigma + 1e-4
+
+
+def test_depth_cap_gpu(rtb):
+    s = rtb.Scene()
+    w = s.flip_normals(s.sphere((0, 0, 0), 10.0, s.lambertian(s.solid(1, 1, 1))))
+    cam = rtb.camera((0, 0, 0), (0, 0, -1), (0, 1, 0), 40.0, 1.0, 0.0, 1.0, 0.0, 1.0)
+    for depth in (0, 3, 50):
+        _, _, st = s.render(w, cam, 32, 32, 4, rtb.default_opts(max_depth=depth, collect_stats=1), want_stats=True,
+                            want_rgb8=False)
+        assert st["segments"] == st["paths"] * (depth + 1) == 32 * 32 * 4 * (depth + 1)
+
+
+# ---- 6. sample sharding (the multi-GPU partition) is exact up to f32 summation order ---------------------
+def test_sample_sharding_sums_to_the_full_image(rtb):
+    nx, ny, ns = 96, 64, 48
+    s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
+    full, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=5), want_rgb8=False)
+    for world in (2, 4, 8):
+        acc = np.zeros_like(full, dtype=np.float64)
+        for rank in range(world):
+            part, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=5, sample_begin=rank, sample_stride=world),
+                                  want_rgb8=False)
+            acc += part
+        np.testing.assert_allclose(acc, full, rtol=2e-5, atol=1e-5)
+    again, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=5), want_rgb8=False)
+    np.testing.assert_allclose(again, full, rtol=2e-5, atol=1e-5)  # reproducible for a fixed seed
+
+
+def test_empty_and_ragged_inputs(rtb):
+    s, w, cam = rtb.Scene.named("two_spheres", 13, 7)
+    p, t = s.closest_hit(w, np.zeros((0, 7)))
+    assert p.shape == (0,)
+    g, rgb8, _ = s.render(w, cam, 13, 7, 3, rtb.default_opts(background=1))  # sizes not multiples of the 8x4 tile
+    assert g.shape == (7, 13, 3) and np.all(g > 0)
+    # an empty world: every ray misses
+    s2 = rtb.Scene()
+    w2 = s2.list([])
+    g2, _, _ = s2.render(w2, cam, 13, 7, 2, rtb.default_opts(background=1))
+    assert np.all(g2 > 0)
+    p, t = s2.closest_hit(w2, rtb.primary_rays(cam, 13, 7))
+    assert np.all(p == -1)
