@@ -32,14 +32,15 @@ namespace rtb {
 
 struct MegaParams {
   int nx, ny;
-  int ns;             // total samples per pixel of the image (for the s < ns bound)
+  int ns;             // total samples per pixel of the image
   int sample_first;   // first sample index this launch renders
   int sample_step;    // distance between consecutive samples of this launch (GPU sharding stride)
   int sample_count;   // samples per pixel in this launch
-  int slices;         // threads per pixel (sample slices) in this launch
+  int slices;         // warps per pixel tile (each takes every slices-th sample of the launch)
   int max_depth;
   float t_min;
   int background;
+  int shade_threshold;  // lanes that must be waiting before the warp runs its shade phase
   uint64_t seed;
 };
 
@@ -49,99 +50,206 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
   return v;
 }
 
+// Lane states of the megakernel's per-warp scheduler, stored in `cur`:
+//   cur >= 0                inner BVH node to test next
+//   CUR_DONE < cur < 0      leaf code ~(first << 3 | count): primitives still to test
+//   CUR_SHADE               traversal finished, waiting for the shade phase
+//   CUR_NEW                 needs a new camera path
+//   CUR_DONE                pool exhausted
+#define CUR_SHADE (-2147483647 - 1)
+#define CUR_NEW (-2147483647)
+#define CUR_DONE (-2147483646)
+
+// k_render_mega — one persistent warp per 8x4 pixel tile (x sample slice).
+//
+// The reference runs   for pixel { for sample { color(ray) } }   with color() recursing up to 50
+// deep (tests/test.rs:62-70, src/color.rs:6-23).  Here a warp owns the pool of
+// (pixel of its tile) x (its samples) paths; every lane carries one path and the warp advances
+// them with a three-phase scheduler chosen by ballot each iteration:
+//   NODE  lanes at an inner BVH node test its two child boxes (node_step)
+//   LEAF  lanes at a leaf test one primitive (intersect_prim)
+//   SHADE lanes whose traversal finished run media + hit record + emitted + scatter, and lanes
+//         whose path ended draw the next path of the pool immediately (no lane waits for a
+//         pixel-mate's longer path; the only tail is the last few paths of the pool)
+// The phase with the most lanes runs (SHADE only once `shade_threshold` lanes wait for it or
+// nothing else is runnable), so each phase's code executes with a well-filled warp instead of
+// the ~7/32 lanes a naive per-thread path loop reaches on these scenes (profiles/).
+// Radiance sums go to a per-warp shared-memory tile and to the accumulation buffer once.
 template <bool kStats>
-__global__ void __launch_bounds__(256) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
-                                                     unsigned long long* __restrict__ stats) {
-  // warp -> 8x4 pixel tile, so the 32 camera rays of a warp start out coherent
-  const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
+                                                        unsigned long long* __restrict__ stats) {
+  __shared__ float s_acc[8][96];
+  __shared__ int s_next[8];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
   const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int tiles_x = (P.nx + 7) >> 3, tiles_y = (P.ny + 3) >> 2;
   const long long tile = warp_global / P.slices;
   const int slice = (int)(warp_global - tile * P.slices);
   const int tx = (int)(tile % tiles_x), ty = (int)(tile / tiles_x);
-  const int i = tx * 8 + (lane & 7);
-  const int row = ty * 4 + (lane >> 3);  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
-  const bool valid = ty < tiles_y && i < P.nx && row < P.ny;
-  const int j = P.ny - 1 - row;
-  const uint32_t pixel = (uint32_t)(row * P.nx + i);
+  const int x0 = tx * 8, y0 = ty * 4;  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
+  const int w_t = min(8, P.nx - x0), h_t = ty < tiles_y ? min(4, P.ny - y0) : 0;
+  const int n_pix = w_t * h_t;
+  const int my_count = slice < P.sample_count ? (P.sample_count - slice + P.slices - 1) / P.slices : 0;
+  const int pool = n_pix * my_count;  // paths this warp renders: id -> (pixel id % n_pix, sample id / n_pix)
+
+  for (int q = lane; q < 96; q += 32) s_acc[wib][q] = 0.0f;
+  if (lane == 0) s_next[wib] = 0;
+  __syncwarp();
 
   Counters cnt = {0, 0, 0};
   TexCounters tc = {{0, 0, 0, 0}};
-  unsigned long long n_paths = 0, n_segments = 0;
+  unsigned long long n_segments = 0;
   unsigned long long n_shade[5] = {0, 0, 0, 0, 0};
 
-  V3f sum = mk(0.f, 0.f, 0.f);
-  if (valid) {
-    int k = slice;  // index into this launch's sample list; this thread takes k, k+slices, ...
-    bool alive = false;
-    RayF ray;
-    V3f thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
-    int depth = 0, self_prim = -1, self_face = 0;
-    PathRng rng;
-    rng.n = 0;
-    for (;;) {
-      if (!alive) {
-        if (k >= P.sample_count) break;
-        const int s = P.sample_first + k * P.sample_step;
-        k += P.slices;
-        rng.init(P.seed, pixel, (uint32_t)s, 0u);
-        ray = camera_ray(cam, i, j, P.nx, P.ny, rng);
-        thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
-        depth = 0, self_prim = -1, self_face = 0;
-        alive = true;
-        if (kStats) n_paths++;
+  RayF ray;
+  ray.o = mk(0.f, 0.f, 0.f), ray.d = mk(0.f, 0.f, 1.f), ray.time = 0.f;
+  RayInv ri = make_ray_inv(ray);
+  float inv_a = 1.0f;
+  Hit best;
+  best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
+  V3f thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
+  int depth = 0, self_prim = -1, self_face = 0, pix_local = 0;
+  uint32_t pixel = 0, sample = 0;
+  int stack[RTB_STACK_DEPTH];
+  int sp = 0;
+  int cur = pool > 0 ? CUR_NEW : CUR_DONE;
+
+  for (;;) {
+    const unsigned m_node = __ballot_sync(0xffffffffu, cur >= 0);
+    const unsigned m_leaf = __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
+    const unsigned m_shade = __ballot_sync(0xffffffffu, cur == CUR_SHADE || cur == CUR_NEW);
+    if ((m_node | m_leaf | m_shade) == 0u) break;
+    const int n_node = __popc(m_node), n_leaf = __popc(m_leaf), n_shade_l = __popc(m_shade);
+
+    if (n_shade_l > 0 && (n_shade_l >= P.shade_threshold || (n_node | n_leaf) == 0)) {
+      // ------------------------------------------------------------------ SHADE phase
+      if (cur == CUR_SHADE || cur == CUR_NEW) {
+        bool need_new = cur == CUR_NEW;
+        if (!need_new) {
+          // the segment's closest surface hit is in `best`; media may pre-empt it
+          n_segments++;
+          int medium = -1;
+          if (sv.n_media > 0)
+            medium = sample_media<kStats>(sv, ray, P.t_min, &best.t, P.seed, pixel, sample, (uint32_t)depth, &cnt);
+          bool ended = true;
+          if (medium >= 0 || best.prim >= 0) {
+            Surface s;
+            if (medium >= 0) {  // src/medium.rs:44-51
+              s.p = madd(best.t, ray.d, ray.o);
+              s.n = mk(1.f, 0.f, 0.f);
+              s.u = 0.f, s.v = 0.f;
+              s.mat = __ldg(&sv.media[medium].mat);
+              self_prim = -1;
+            } else {
+              s = finalize_hit(sv, sv.prims, ray, best);
+              self_prim = best.prim, self_face = best.face;
+            }
+            const int4 m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
+            if (kStats) n_shade[m.x]++;
+            if (m.x == RTB_MAT_DIFFUSE_LIGHT)  // emitted, src/color.rs:8 (zero for every other material)
+              rad = rad + thr * texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
+            if (depth < P.max_depth) {  // src/color.rs:9
+              const Rand4 rnd = rand4(P.seed, (uint32_t)depth, pixel, sample, 1u);
+              V3f atten;
+              if (scatter<kStats>(sv, m.x, m.y, __int_as_float(m.z), s, ray, rnd, &atten, &tc)) {
+                thr = thr * atten;
+                ++depth;
+                ended = false;
+              }
+            }
+          } else {
+            rad = rad + thr * background_color(P.background, ray.d);  // miss, src/color.rs:17-22
+          }
+          if (ended) {
+            if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
+              float* a = &s_acc[wib][pix_local * 3];
+              atomicAdd(a, rad.x);
+              atomicAdd(a + 1, rad.y);
+              atomicAdd(a + 2, rad.z);
+            }
+            need_new = true;
+          }
+        }
+        // lanes whose path ended take the next paths of the warp's pool, in lane order
+        const unsigned m_need = __ballot_sync(m_shade, need_new);
+        if (need_new) {
+          const int base = s_next[wib];
+          const int id = base + __popc(m_need & lt_mask);
+          __syncwarp(m_need);
+          if ((m_need & lt_mask) == 0u) s_next[wib] = base + __popc(m_need);
+          if (id < pool) {
+            pix_local = id % n_pix;
+            const int k = slice + (id / n_pix) * P.slices;  // index in this launch's sample list
+            sample = (uint32_t)(P.sample_first + k * P.sample_step);
+            const int lx = pix_local % w_t, ly = pix_local / w_t;
+            const int i = x0 + lx, row = y0 + ly;
+            pixel = (uint32_t)(row * P.nx + i);
+            ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.seed, pixel, sample);
+            thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
+            depth = 0, self_prim = -1, self_face = 0;
+          } else {
+            cur = CUR_DONE;
+          }
+        }
+        if (cur != CUR_DONE) {  // start the next segment: world.hit(ray, t_min, MAX), src/color.rs:7
+          ri = make_ray_inv(ray);
+          inv_a = rcp_fast(dot(ray.d, ray.d));
+          best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
+          sp = 0;
+          cur = sv.root;
+        }
       }
-      // ---- one segment: world.hit(ray, t_min, MAX)  (src/color.rs:7)
-      n_segments++;
-      Hit h = trace_closest<kStats>(sv, ray, P.t_min, self_prim, self_face, &cnt);
-      int medium = -1;
-      if (sv.n_media > 0) medium = sample_media<kStats>(sv, ray, P.t_min, &h.t, rng, &cnt);
-      if (medium < 0 && h.prim < 0) {  // miss
-        V3f bg = background_color(P.background, ray.d);
-        rad = rad + thr * bg;
-        sum = sum + rad;
-        alive = false;
-        continue;
+    } else if (n_node >= n_leaf) {
+      // ------------------------------------------------------------------ NODE phase
+      if (cur >= 0) {
+        if (kStats) cnt.node_tests++;
+        int next, push;
+        const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+        if (nh == 2) stack[sp++] = push;
+        if (nh == 0) next = sp > 0 ? stack[--sp] : CUR_SHADE;
+        cur = next;
       }
-      Surface s;
-      if (medium >= 0) {  // src/medium.rs:44-51
-        s.p = madd(h.t, ray.d, ray.o);
-        s.n = mk(1.f, 0.f, 0.f);
-        s.u = 0.f, s.v = 0.f;
-        s.mat = __ldg(&sv.media[medium].mat);
-        self_prim = -1;
-      } else {
-        s = finalize_hit(sv, sv.prims, ray, h);
-        self_prim = h.prim, self_face = h.face;
-      }
-      const int4 m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
-      if (kStats) n_shade[m.x]++;
-      if (m.x == RTB_MAT_DIFFUSE_LIGHT)  // emitted, src/color.rs:8 (zero for every other material)
-        rad = rad + thr * texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
-      V3f atten;
-      if (depth < P.max_depth && scatter<kStats>(sv, m.x, m.y, __int_as_float(m.z), s, ray, rng, &atten, &tc)) {
-        thr = thr * atten;
-        ++depth;
-      } else {
-        sum = sum + rad;
-        alive = false;
+    } else {
+      // ------------------------------------------------------------------ LEAF phase
+      if (cur < 0 && cur > CUR_DONE) {
+        const unsigned code = ~(unsigned)cur;
+        const int pi = (int)(code >> 3);
+        int count = (int)(code & 7u);
+        if (count > 0) {
+          float t;
+          int face, id;
+          if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, P.t_min, best.t, pi == self_prim, self_face, &t,
+                                     &face, &id, &cnt) &&
+              (t < best.t || id > best.id)) {
+            best.t = t, best.prim = pi, best.face = face, best.id = id;
+          }
+          --count;
+          cur -= 7;  // first + 1, count - 1
+        }
+        if (count == 0) cur = sp > 0 ? stack[--sp] : CUR_SHADE;
       }
     }
-    float* a = accum + 3ull * pixel;
-    atomicAdd(a, sum.x);
-    atomicAdd(a + 1, sum.y);
-    atomicAdd(a + 2, sum.z);
+  }
+
+  __syncwarp();
+  for (int q = lane; q < n_pix * 3; q += 32) {
+    const float v = s_acc[wib][q];
+    if (v != 0.0f) {
+      const int pl = q / 3, c = q - pl * 3;
+      const int row = y0 + pl / w_t, i = x0 + pl % w_t;
+      atomicAdd(accum + 3ull * ((size_t)row * P.nx + i) + c, v);
+    }
   }
   // counters: one atomic per warp
   unsigned long long v = warp_sum(n_segments);
   if (lane == 0 && v) atomicAdd(stats + 1, v);
   if (kStats) {
-    unsigned long long vals[14] = {n_paths,    0,          cnt.node_tests, cnt.prim_tests, cnt.medium_tests,
+    unsigned long long vals[14] = {0,          0,          cnt.node_tests, cnt.prim_tests, cnt.medium_tests,
                                    n_shade[0], n_shade[1], n_shade[2],     n_shade[3],     n_shade[4],
                                    tc.n[0],    tc.n[1],    tc.n[2],        tc.n[3]};
 #pragma unroll
-    for (int q = 0; q < 14; ++q) {
-      if (q == 1) continue;
+    for (int q = 2; q < 14; ++q) {
       unsigned long long w = warp_sum(vals[q]);
       if (lane == 0 && w) atomicAdd(stats + q, w);
     }
@@ -317,6 +425,7 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
+    P.shade_threshold = o.reserved[0] > 0 ? o.reserved[0] : 12;
     const long long warps = tiles * P.slices;
     const int block = 256;
     const long long blocks = (warps * 32 + block - 1) / block;

@@ -1,7 +1,7 @@
 // trace.cuh — device-side building blocks shared by the megakernel and the wavefront
-// kernels: RNG stream, ray/primitive intersection, BVH traversal, constant media, textures
-// and material scattering.  f32 throughout; each routine cites the f64 reference code whose
-// result it reproduces.
+// kernels: RNG draws, ray/primitive intersection, BVH traversal, constant media, textures and
+// material scattering.  f32 throughout; each routine cites the f64 reference code whose result
+// it reproduces.
 #pragma once
 #include <cuda_runtime.h>
 #include <math_constants.h>
@@ -36,32 +36,57 @@ __device__ __forceinline__ void set_comp(V3f& v, int axis, float s) {
 __device__ __forceinline__ float4 ldg4(const f4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ int4 ldg4i(const i4* p) { return __ldg(reinterpret_cast<const int4*>(p)); }
 
-// ---- RNG stream of one path -------------------------------------------------------------------
-struct PathRng {
-  uint32_t k0, k1, pixel, sample;
-  uint32_t n;  // draws consumed so far
-  u4 buf;
-  __device__ __forceinline__ void init(uint64_t seed, uint32_t pixel_, uint32_t sample_, uint32_t n0) {
-    k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32), pixel = pixel_, sample = sample_;
-    n = n0;
-    if (n0 & 3u) buf = philox4x32_10(u4{n0 >> 2, pixel, sample, 0u}, k0, k1);
-  }
-  __device__ __forceinline__ float next() {
-    uint32_t i = n & 3u;
-    if (i == 0u) buf = philox4x32_10(u4{n >> 2, pixel, sample, 0u}, k0, k1);
-    ++n;
-    uint32_t r = i == 0u ? buf.x : (i == 1u ? buf.y : (i == 2u ? buf.z : buf.w));
-    return u01(r);
-  }
+// Single-instruction SFU forms (MUFU.RCP / RSQ / SQRT / EX2 / LG2, <= 2 ulp).  The f64 reference
+// is matched statistically and through closest-hit IDs, not bit-wise, so the IEEE-rounded
+// division / sqrt sequences (and their slow-path subroutines) buy nothing here.
+__device__ __forceinline__ float rcp_fast(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float sqrt_fast(float x) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float rsqrt_fast(float x) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float cbrt_fast01(float x) {  // x in (0,1): 2^(log2(x)/3)
+  return exp2f(__log2f(x) * (1.0f / 3.0f));
+}
+// sin(x) for |x| up to ~1e5: two-constant Cody-Waite reduction to [-pi, pi], then MUFU.SIN
+__device__ __forceinline__ float sin_reduced(float x) {
+  float k = rintf(x * 0.15915494309189535f);
+  float r = fmaf(-k, 6.2831854820251465f, x);  // 2*pi rounded to f32
+  r = fmaf(-k, -1.7484555e-7f, r);              // 2*pi - fl(2*pi)
+  return __sinf(r);
+}
+
+// ---- RNG: one Philox4x32-10 call = four U(0,1) draws ------------------------------------------
+// counter = (block, pixel, sample, purpose), key = seed.  purpose 0: block 0 = camera
+// (jitter_u, jitter_v, lens_r, lens_phi), block 1 = (time,-,-,-); purpose 1: block = depth,
+// the scatter draws of that bounce (ball x3, schlick); purpose 2 + g: block = depth, the
+// free-flight draws of media 4g .. 4g+3 on that segment.
+struct Rand4 {
+  float x, y, z, w;
 };
+__device__ __forceinline__ float u01_open(uint32_t v) { return ((float)(v >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+__device__ __forceinline__ Rand4 rand4(uint64_t seed, uint32_t block, uint32_t pixel, uint32_t sample, uint32_t purpose) {
+  u4 r = philox4x32_10(u4{block, pixel, sample, purpose}, (uint32_t)seed, (uint32_t)(seed >> 32));
+  // (k + 0.5) * 2^-24 lies strictly inside (0,1): no zero-length ball sample, no log(0)
+  return Rand4{u01_open(r.x), u01_open(r.y), u01_open(r.z), u01_open(r.w)};
+}
 
 // uniform in the unit ball == the distribution of the rejection loop at src/util.rs:4-13,
-// sampled directly (3 draws, no divergence)
-__device__ __forceinline__ V3f sample_unit_ball(PathRng& rng) {
-  float z = 1.0f - 2.0f * rng.next();
-  float phi = (2.0f * rng.next() - 1.0f) * CUDART_PI_F;
-  float r = cbrtf(rng.next());
-  float s = sqrtf(fmaxf(0.0f, 1.0f - z * z)) * r;
+// sampled directly from 3 draws (no divergence)
+__device__ __forceinline__ V3f sample_unit_ball(float r0, float r1, float r2) {
+  float z = 1.0f - 2.0f * r0;
+  float phi = (2.0f * r1 - 1.0f) * CUDART_PI_F;
+  float r = cbrt_fast01(r2);
+  float s = sqrt_fast(fmaxf(0.0f, 1.0f - z * z)) * r;
   float sn, cs;
   __sincosf(phi, &sn, &cs);
   return mk(s * cs, s * sn, r * z);
@@ -77,6 +102,7 @@ struct Hit {
   float t;
   int prim;  // index into prims (or bprims for boundary queries); -1 = none
   int face;  // BOX: face 0..5 in the order of src/cube.rs:21-74
+  int id;    // primitive ID of the hit (first ID + face), for the tie rule
 };
 
 __device__ __forceinline__ V3f xf_point(const DXform& x, V3f p) {  // local = M p + b
@@ -130,15 +156,19 @@ struct Counters {
 //   Rect:   src/rect.rs:39-69 (all comparisons inclusive).
 //   Box:    the six Rects of src/cube.rs:21-74 scanned by HittableList::hit == nearest of
 //           {slab entry, slab exit} inside [t_min, t_max].
+// Plane distances are always (k - o) * rcp(d), in Rect and Box alike, so coincident planes
+// (a cube standing on a floor rect) produce bit-identical t and the ID tie rule can apply.
 template <bool kStats>
 __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXform* __restrict__ xforms,
                                                const RayF& ray, float inv_a, float t_min, float t_max, bool self,
-                                               int self_face, float* t_out, int* face_out, Counters* cnt) {
+                                               int self_face, float* t_out, int* face_out, int* id_out, Counters* cnt) {
   if (kStats) cnt->prim_tests++;
   const float4 A = ldg4(&prims[pi].a);
   const float4 B = ldg4(&prims[pi].b);
   const int4 C = ldg4i(&prims[pi].c);
   const int type = RTB_PRIM_TYPE(C.x);
+  *id_out = C.z;
+  *face_out = 0;
   if (type <= DP_MOVING_SPHERE) {
     V3f ctr = sphere_center(A, B, C, ray.time);
     V3f oc = ray.o - ctr;
@@ -147,17 +177,17 @@ __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, 
     float t;
     if (self) {
       t = 2.0f * tc;  // roots are 0 and -2b/a
-      if (t < t_max && t > t_min) { *t_out = t; return true; }
-      return false;
+      *t_out = t;
+      return t < t_max && t > t_min;
     }
     V3f l = madd(tc, ray.d, oc);
     float disc = fmaf(A.w, A.w, -dot(l, l));
     if (disc > 0.0f) {
-      float h = sqrtf(disc * inv_a);
+      float h = sqrt_fast(disc * inv_a);
       t = tc - h;
-      if (t < t_max && t > t_min) { *t_out = t; return true; }
-      t = tc + h;
-      if (t < t_max && t > t_min) { *t_out = t; return true; }
+      if (!(t < t_max && t > t_min)) t = tc + h;
+      *t_out = t;
+      return t < t_max && t > t_min;
     }
     return false;
   }
@@ -173,7 +203,7 @@ __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, 
     if (self) return false;  // a ray leaving a plane never meets it again
     const int plane = RTB_PRIM_PLANE(C.x);
     const int k_axis = plane, a_axis = plane == 2 ? 0 : plane + 1, b_axis = plane == 0 ? 2 : plane - 1;
-    float t = (B.x - comp(o, k_axis)) / comp(d, k_axis);
+    float t = (B.x - comp(o, k_axis)) * rcp_fast(comp(d, k_axis));
     if (t < t_min || t > t_max) return false;
     float x = fmaf(t, comp(d, a_axis), comp(o, a_axis));
     float y = fmaf(t, comp(d, b_axis), comp(o, b_axis));
@@ -182,7 +212,7 @@ __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, 
     return true;
   }
   // DP_BOX
-  float ix = 1.0f / d.x, iy = 1.0f / d.y, iz = 1.0f / d.z;
+  float ix = rcp_fast(d.x), iy = rcp_fast(d.y), iz = rcp_fast(d.z);
   float tx0 = (A.x - o.x) * ix, tx1 = (B.x - o.x) * ix;
   float ty0 = (A.y - o.y) * iy, ty1 = (B.y - o.y) * iy;
   float tz0 = (A.z - o.z) * iz, tz1 = (B.z - o.z) * iz;
@@ -205,21 +235,66 @@ __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, 
   float t_exit = fminf(fminf(fx, fy), fz);
   if (!(t_enter <= t_exit)) return false;
   // candidates in list-scan terms: the entry face, then the exit face
-  if (t_enter >= t_min && t_enter <= t_max) {
-    int ax = (nx >= ny && nx >= nz) ? 0 : (ny >= nz ? 1 : 2);
-    float dk = comp(d, ax);
+  const bool use_enter = t_enter >= t_min && t_enter <= t_max;
+  const bool use_exit = t_exit >= t_min && t_exit <= t_max;
+  if (!use_enter && !use_exit) return false;
+  int ax;
+  bool is_min;
+  if (use_enter) {
+    ax = (nx >= ny && nx >= nz) ? 0 : (ny >= nz ? 1 : 2);
+    is_min = comp(d, ax) > 0.0f;  // entering through the min plane when d > 0
     *t_out = t_enter;
-    *face_out = ((2 - ax) << 1) | (dk > 0.0f ? 1 : 0);  // entering through the min plane when d > 0
-    return true;
-  }
-  if (t_exit >= t_min && t_exit <= t_max) {
-    int ax = (fx <= fy && fx <= fz) ? 0 : (fy <= fz ? 1 : 2);
-    float dk = comp(d, ax);
+  } else {
+    ax = (fx <= fy && fx <= fz) ? 0 : (fy <= fz ? 1 : 2);
+    is_min = !(comp(d, ax) > 0.0f);  // leaving through the max plane when d > 0
     *t_out = t_exit;
-    *face_out = ((2 - ax) << 1) | (dk > 0.0f ? 0 : 1);  // leaving through the max plane when d > 0
-    return true;
   }
-  return false;
+  const int face = ((2 - ax) << 1) | (is_min ? 1 : 0);
+  *face_out = face;
+  *id_out = C.z + face;
+  return true;
+}
+
+// ---- BVH node step -----------------------------------------------------------------------------
+struct RayInv {  // per-ray constants of the slab test
+  float idx, idy, idz, oodx, oody, oodz;
+};
+__device__ __forceinline__ RayInv make_ray_inv(const RayF& ray) {
+  auto safe_inv = [](float v) { return rcp_fast(fabsf(v) > 1e-20f ? v : copysignf(1e-20f, v)); };
+  RayInv r;
+  r.idx = safe_inv(ray.d.x), r.idy = safe_inv(ray.d.y), r.idz = safe_inv(ray.d.z);
+  r.oodx = ray.o.x * r.idx, r.oody = ray.o.y * r.idy, r.oodz = ray.o.z * r.idz;
+  return r;
+}
+
+// Tests both children of inner node `cur` against (t_min, t_best).  Returns the number of
+// children hit (0, 1, 2); *next = the child to visit next (the nearer one), *push = the other
+// (valid when 2 is returned).
+__device__ __forceinline__ int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
+                                         int* next, int* push) {
+  const DNode* nd = nodes + cur;
+  const float4 n0 = ldg4(&nd->n0), n1 = ldg4(&nd->n1), n2 = ldg4(&nd->n2);
+  const int4 n3 = ldg4i(&nd->n3);
+  float c0lox = fmaf(n0.x, ri.idx, -ri.oodx), c0hix = fmaf(n0.y, ri.idx, -ri.oodx);
+  float c0loy = fmaf(n0.z, ri.idy, -ri.oody), c0hiy = fmaf(n0.w, ri.idy, -ri.oody);
+  float c0loz = fmaf(n2.x, ri.idz, -ri.oodz), c0hiz = fmaf(n2.y, ri.idz, -ri.oodz);
+  float c1lox = fmaf(n1.x, ri.idx, -ri.oodx), c1hix = fmaf(n1.y, ri.idx, -ri.oodx);
+  float c1loy = fmaf(n1.z, ri.idy, -ri.oody), c1hiy = fmaf(n1.w, ri.idy, -ri.oody);
+  float c1loz = fmaf(n2.z, ri.idz, -ri.oodz), c1hiz = fmaf(n2.w, ri.idz, -ri.oodz);
+  float tn0 = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
+  float tf0 = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), t_best));
+  float tn1 = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
+  float tf1 = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), t_best));
+  const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
+  const bool swap = tn1 < tn0;
+  const int c0 = n3.x, c1 = n3.y;
+  if (h0 && h1) {
+    *next = swap ? c1 : c0;
+    *push = swap ? c0 : c1;
+    return 2;
+  }
+  *next = h0 ? c0 : c1;
+  return (h0 || h1) ? 1 : 0;
 }
 
 #define RTB_STACK_DEPTH 64
@@ -227,60 +302,41 @@ __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, 
 // Closest surface hit over (t_min, +inf): the result of world.hit(ray, 0.001, f64::MAX)
 // (src/color.rs:7) restricted to surfaces.  Stack-based traversal of the two-child BVH,
 // near child first, far child pushed, the query interval shrinking with every accepted hit.
+// Exact ties: Rect accepts t == t_max (src/rect.rs:46) so in the reference's list scan a LATER
+// planar primitive replaces an earlier one at equal t (Q23; e.g. cornell_box's two floors and
+// the cube bottoms resting on them); later == higher primitive ID, which is what wins here.
 template <bool kStats>
 __device__ __forceinline__ Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int self_prim,
                                              int self_face, Counters* cnt) {
   Hit best;
-  best.t = CUDART_INF_F, best.prim = -1, best.face = 0;
-  const float inv_a = 1.0f / dot(ray.d, ray.d);
-  auto safe_inv = [](float v) { return 1.0f / (fabsf(v) > 1e-20f ? v : copysignf(1e-20f, v)); };
-  const float idx = safe_inv(ray.d.x), idy = safe_inv(ray.d.y), idz = safe_inv(ray.d.z);
-  const float oodx = ray.o.x * idx, oody = ray.o.y * idy, oodz = ray.o.z * idz;
-
+  best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
+  const float inv_a = rcp_fast(dot(ray.d, ray.d));
+  const RayInv ri = make_ray_inv(ray);
   int stack[RTB_STACK_DEPTH];
   int sp = 0;
   int cur = sv.root;
   for (;;) {
     while (cur >= 0) {
       if (kStats) cnt->node_tests++;
-      const DNode* nd = sv.nodes + cur;
-      const float4 n0 = ldg4(&nd->n0), n1 = ldg4(&nd->n1), n2 = ldg4(&nd->n2);
-      const int4 n3 = ldg4i(&nd->n3);
-      float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
-      float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
-      float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
-      float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
-      float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
-      float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
-      float tn0 = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), t_min));
-      float tf0 = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), best.t));
-      float tn1 = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), t_min));
-      float tf1 = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), best.t));
-      const bool h0 = tn0 <= tf0, h1 = tn1 <= tf1;
-      if (h0 && h1) {
-        int near = n3.x, far = n3.y;
-        if (tn1 < tn0) near = n3.y, far = n3.x;
-        stack[sp++] = far;
-        cur = near;
-      } else if (h0) {
-        cur = n3.x;
-      } else if (h1) {
-        cur = n3.y;
-      } else {
+      int next, push;
+      int nh = node_step(sv.nodes, cur, ri, t_min, best.t, &next, &push);
+      if (nh == 2) stack[sp++] = push;
+      if (nh == 0) {
         if (sp == 0) return best;
-        cur = stack[--sp];
+        next = stack[--sp];
       }
+      cur = next;
     }
-    // leaf
     const unsigned code = ~(unsigned)cur;
     const int first = (int)(code >> 3), count = (int)(code & 7u);
     for (int i = 0; i < count; ++i) {
       const int pi = first + i;
       float t;
-      int face = 0;
+      int face, id;
       if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, t_min, best.t, pi == self_prim, self_face, &t,
-                                 &face, cnt)) {
-        best.t = t, best.prim = pi, best.face = face;
+                                 &face, &id, cnt) &&
+          (t < best.t || id > best.id)) {
+        best.t = t, best.prim = pi, best.face = face, best.id = id;
       }
     }
     if (sp == 0) return best;
@@ -293,7 +349,6 @@ struct Surface {
   V3f p, n;  // world-space hit point and shading normal (FlipNormals applied)
   float u, v;
   int mat;
-  int prim_id;
 };
 
 __device__ __forceinline__ void sphere_uv(V3f n, float* u, float* v) {  // src/sphere.rs:9-15 (Q5: FRAC_2_PI)
@@ -315,14 +370,12 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
   const int type = RTB_PRIM_TYPE(C.x);
   const int xi = RTB_PRIM_XFORM(C.x);
   s.mat = C.y;
-  s.prim_id = C.z;
   s.u = 0.0f, s.v = 0.0f;
   const bool need_uv = __ldg(&sv.mats[C.y].needs_uv) != 0;
   if (type <= DP_MOVING_SPHERE) {
     V3f ctr = sphere_center(A, B, C, ray.time);
     s.p = madd(h.t, ray.d, ray.o);
-    float inv_r = 1.0f / A.w;
-    s.n = inv_r * (s.p - ctr);
+    s.n = rcp_fast(A.w) * (s.p - ctr);
     if (need_uv) {
       V3f nl = s.n;
       if (xi != 0) nl = xf_vec(load_xform(sv.xforms, xi), s.n);  // uv is taken in the sphere's own frame
@@ -338,23 +391,25 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
     }
     V3f pl = madd(h.t, d, o);
     int k_axis;
-    float a0, b0, a1, b1;  // the face's (x0,y0,x1,y1) in its (a,b) axes
+    bool is_min = false;
     if (type == DP_RECT) {
       k_axis = RTB_PRIM_PLANE(C.x);
       set_comp(pl, k_axis, B.x);  // the hit point lies on the plane exactly
-      a0 = A.x, b0 = A.y, a1 = A.z, b1 = A.w;
     } else {
       k_axis = 2 - (h.face >> 1);
-      const bool is_min = h.face & 1;
+      is_min = h.face & 1;
       set_comp(pl, k_axis, is_min ? comp(mk(A.x, A.y, A.z), k_axis) : comp(mk(B.x, B.y, B.z), k_axis));
-      s.prim_id += h.face;
-      const int aa = k_axis == 2 ? 0 : k_axis + 1, bb = k_axis == 0 ? 2 : k_axis - 1;
-      a0 = comp(mk(A.x, A.y, A.z), aa), b0 = comp(mk(A.x, A.y, A.z), bb);
-      a1 = comp(mk(B.x, B.y, B.z), aa), b1 = comp(mk(B.x, B.y, B.z), bb);
     }
-    if (need_uv) {
+    if (need_uv) {  // src/rect.rs:54-55 with the face's (x0,y0,x1,y1) in its (a,b) axes
       const int aa = k_axis == 2 ? 0 : k_axis + 1, bb = k_axis == 0 ? 2 : k_axis - 1;
-      s.u = (comp(pl, aa) - a0) / (a1 - a0);  // src/rect.rs:54-55
+      float a0, b0, a1, b1;
+      if (type == DP_RECT) {
+        a0 = A.x, b0 = A.y, a1 = A.z, b1 = A.w;
+      } else {
+        a0 = comp(mk(A.x, A.y, A.z), aa), b0 = comp(mk(A.x, A.y, A.z), bb);
+        a1 = comp(mk(B.x, B.y, B.z), aa), b1 = comp(mk(B.x, B.y, B.z), bb);
+      }
+      s.u = (comp(pl, aa) - a0) / (a1 - a0);
       s.v = (comp(pl, bb) - b0) / (b1 - b0);
     }
     V3f nl = mk(k_axis == 0 ? 1.0f : 0.0f, k_axis == 1 ? 1.0f : 0.0f, k_axis == 2 ? 1.0f : 0.0f);  // always +e_k (Q9)
@@ -371,53 +426,52 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
 }
 
 // ---- constant media: src/medium.rs:28-56 -------------------------------------------------------
-// boundary.hit(ray, lo, +inf) over the medium's boundary primitives, list order, closest wins.
-template <bool kStats>
-__device__ __forceinline__ bool boundary_hit(const SceneView& sv, const DMedium& m, const RayF& ray, float inv_a, float lo,
-                                             float* t_out, Counters* cnt) {
-  float best = CUDART_INF_F;
-  bool any = false;
-  for (int i = 0; i < m.count; ++i) {
-    float t;
-    int face;
-    if (intersect_prim<kStats>(sv.bprims, m.first + i, sv.xforms, ray, inv_a, lo, best, false, 0, &t, &face, cnt)) {
-      best = t;
-      any = true;
-    }
-  }
-  *t_out = best;
-  return any;
-}
-
 // Runs every medium against the ray after the surface query.  Per medium (reference order):
-// hit1 = boundary.hit(-MAX, MAX); hit2 = boundary.hit(hit1.t + 1e-4, MAX); clamp to
-// [t_min, closest_so_far]; exponential free flight.  Independent exponentials clipped to the
-// running closest hit give the same distribution as the reference's list scan (Q13).
-// Returns the index of the medium that scattered, or -1.
+// hit1 = boundary.hit(-MAX, MAX); hit2 = boundary.hit(hit1.t + 1e-4, MAX) — each the closest
+// boundary primitive in list order; clamp to [t_min, closest_so_far]; exponential free flight.
+// Independent exponentials clipped to the running closest hit give the same distribution as
+// the reference's list scan (Q13).  Returns the index of the medium that scattered, or -1.
 template <bool kStats>
 __device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray, float t_min, float* t_closest,
-                                            PathRng& rng, Counters* cnt) {
+                                            uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t depth, Counters* cnt) {
   int which = -1;
   const float a = dot(ray.d, ray.d);
-  const float inv_a = 1.0f / a;
-  const float len = sqrtf(a);
+  const float inv_a = rcp_fast(a);
+  const float inv_len = rsqrt_fast(a);
+  const float len = a * inv_len;
+  Rand4 rnd = rand4(seed, depth, pixel, sample, 2u);
   for (int mi = 0; mi < sv.n_media; ++mi) {
     if (kStats) cnt->medium_tests++;
-    DMedium m;
-    {
-      int4 raw = __ldg(reinterpret_cast<const int4*>(sv.media + mi));
-      m.first = raw.x, m.count = raw.y, m.mat = raw.z, m.neg_inv_density = __int_as_float(raw.w);
+    if (mi && (mi & 3) == 0) rnd = rand4(seed, depth, pixel, sample, 2u + (uint32_t)(mi >> 2));
+    const float xi = (mi & 3) == 0 ? rnd.x : ((mi & 3) == 1 ? rnd.y : ((mi & 3) == 2 ? rnd.z : rnd.w));
+    const int4 raw = __ldg(reinterpret_cast<const int4*>(sv.media + mi));
+    const int first = raw.x, count = raw.y;
+    float t1 = 0.0f, t2 = 0.0f;
+    bool ok = true;
+#pragma unroll 1
+    for (int pass = 0; pass < 2 && ok; ++pass) {
+      const float lo = pass == 0 ? -CUDART_INF_F : t1 + 0.0001f;
+      float best = CUDART_INF_F;
+      bool any = false;
+      for (int i = 0; i < count; ++i) {
+        float t;
+        int face, id;
+        if (intersect_prim<kStats>(sv.bprims, first + i, sv.xforms, ray, inv_a, lo, best, false, 0, &t, &face, &id, cnt)) {
+          best = t;
+          any = true;
+        }
+      }
+      ok = any;
+      if (pass == 0) t1 = best; else t2 = best;
     }
-    float t1, t2;
-    if (!boundary_hit<kStats>(sv, m, ray, inv_a, -CUDART_INF_F, &t1, cnt)) continue;
-    if (!boundary_hit<kStats>(sv, m, ray, inv_a, t1 + 0.0001f, &t2, cnt)) continue;
+    if (!ok) continue;
     if (t1 < t_min) t1 = t_min;
     if (t2 > *t_closest) t2 = *t_closest;
     if (t1 < t2) {
       float distance_inside = (t2 - t1) * len;
-      float hit_distance = m.neg_inv_density * __logf(rng.next());
+      float hit_distance = __int_as_float(raw.w) * __logf(xi);  // -(1/density) * ln(xi)
       if (hit_distance < distance_inside) {
-        *t_closest = t1 + hit_distance / len;
+        *t_closest = fmaf(hit_distance, inv_len, t1);
         which = mi;
       }
     }
@@ -470,6 +524,10 @@ struct TexCounters {
   unsigned long long n[4];
 };
 
+// sign(sin(10 x)) == parity of floor(10 x / pi): the checker only needs the sign of the
+// product of three sines (src/texture.rs:41-42)
+__device__ __forceinline__ int sin10_negative(float x) { return ((int)floorf(x * 3.1830988618379067f)) & 1; }
+
 template <bool kStats>
 __device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p, TexCounters* tc) {
   for (;;) {
@@ -477,15 +535,15 @@ __device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float
     const int type = hd.x;
     if (kStats) tc->n[type & 3]++;
     if (type == RTB_TEX_CHECKER) {  // src/texture.rs:40-47: product of three sines < 0 -> `odd`
-      float s = sinf(10.0f * p.x) * sinf(10.0f * p.y) * sinf(10.0f * p.z);
-      tex = s < 0.0f ? hd.y : hd.z;
+      const int neg = sin10_negative(p.x) ^ sin10_negative(p.y) ^ sin10_negative(p.z);
+      tex = neg ? hd.y : hd.z;
       continue;
     }
     const float4 col = __ldg(reinterpret_cast<const float4*>(sv.texs + tex) + 1);
     if (type == RTB_TEX_SOLID) return mk(col.x, col.y, col.z);
     if (type == RTB_TEX_NOISE) {  // src/texture.rs:66-70
       float t = perlin_turb(sv.perlin + hd.y, p);
-      float g = 0.5f * (1.0f + sinf(fmaf(col.w, p.x, 5.0f * t)));
+      float g = 0.5f * (1.0f + sin_reduced(fmaf(col.w, p.x, 5.0f * t)));
       return mk(g, g, g);
     }
     // RTB_TEX_IMAGE, src/texture.rs:87-107: saturating casts, clamp high, nearest texel
@@ -506,85 +564,76 @@ __device__ __forceinline__ V3f reflect(V3f v, V3f n) { return v - (2.0f * dot(v,
 
 // Material::scatter.  Returns false when the path ends (DiffuseLight, absorbed Metal).
 // On success `ray` becomes the scattered ray (origin = hit.p, same time) and *atten the albedo.
+// rnd: the four draws of this bounce (ball x3, schlick).
 template <bool kStats>
 __device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int mat_tex, float mat_param, const Surface& s,
-                                        RayF& ray, PathRng& rng, V3f* atten, TexCounters* tc) {
-  switch (mat_type) {
-    case RTB_MAT_LAMBERTIAN: {  // :49-53  target - p = normal + ball
-      V3f dir = s.n + sample_unit_ball(rng);
-      *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
-      ray.o = s.p, ray.d = dir;
-      return true;
+                                        RayF& ray, const Rand4& rnd, V3f* atten, TexCounters* tc) {
+  if (mat_type == RTB_MAT_DIFFUSE_LIGHT) return false;  // :144-146
+  if (mat_type == RTB_MAT_DIELECTRIC) {                 // :106-126
+    *atten = mk(1.0f, 1.0f, 1.0f);
+    const float ref_idx = mat_param;
+    const float ddn = dot(ray.d, s.n);
+    const float inv_len = rsqrt_fast(dot(ray.d, ray.d));
+    V3f outward_normal;
+    float ni_over_nt, cosine;
+    if (ddn > 0.0f) {
+      cosine = ref_idx * ddn * inv_len;
+      outward_normal = -s.n;
+      ni_over_nt = ref_idx;
+    } else {
+      cosine = -ddn * inv_len;
+      outward_normal = s.n;
+      ni_over_nt = rcp_fast(ref_idx);
     }
-    case RTB_MAT_METAL: {  // :76-86
-      float inv_len = rsqrtf(dot(ray.d, ray.d));
-      V3f reflected = reflect(inv_len * ray.d, s.n);
-      if (mat_param > 0.0f) reflected = madd(mat_param, sample_unit_ball(rng), reflected);
-      if (dot(reflected, s.n) > 0.0f) {
-        *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
-        ray.o = s.p, ray.d = reflected;
-        return true;
-      }
-      return false;
+    // refract(), :13-23
+    V3f uv = inv_len * ray.d;
+    float dt = dot(uv, outward_normal);
+    float discriminant = 1.0f - ni_over_nt * ni_over_nt * (1.0f - dt * dt);
+    V3f dir = reflect(ray.d, s.n);  // un-normalised d, unflipped hit.normal (Q14)
+    if (discriminant > 0.0f) {
+      float r0 = (1.0f - ref_idx) * rcp_fast(1.0f + ref_idx);  // schlick(), :25-28
+      r0 = r0 * r0;
+      float m = 1.0f - cosine;
+      float m2 = m * m;
+      float reflect_prob = r0 + (1.0f - r0) * (m2 * m2 * m);
+      if (rnd.w >= reflect_prob) dir = ni_over_nt * (uv - dt * outward_normal) - sqrt_fast(discriminant) * outward_normal;
     }
-    case RTB_MAT_DIELECTRIC: {  // :106-126
-      *atten = mk(1.0f, 1.0f, 1.0f);
-      const float ref_idx = mat_param;
-      const float ddn = dot(ray.d, s.n);
-      const float inv_len = rsqrtf(dot(ray.d, ray.d));
-      V3f outward_normal;
-      float ni_over_nt, cosine;
-      if (ddn > 0.0f) {
-        cosine = ref_idx * ddn * inv_len;
-        outward_normal = -s.n;
-        ni_over_nt = ref_idx;
-      } else {
-        cosine = -ddn * inv_len;
-        outward_normal = s.n;
-        ni_over_nt = 1.0f / ref_idx;
-      }
-      // refract(), :13-23
-      V3f uv = inv_len * ray.d;
-      float dt = dot(uv, outward_normal);
-      float discriminant = 1.0f - ni_over_nt * ni_over_nt * (1.0f - dt * dt);
-      if (discriminant > 0.0f) {
-        float r0 = (1.0f - ref_idx) / (1.0f + ref_idx);  // schlick(), :25-28
-        r0 = r0 * r0;
-        float m = 1.0f - cosine;
-        float m2 = m * m;
-        float reflect_prob = r0 + (1.0f - r0) * (m2 * m2 * m);
-        if (rng.next() >= reflect_prob) {
-          V3f refracted = ni_over_nt * (uv - dt * outward_normal) - sqrtf(discriminant) * outward_normal;
-          ray.o = s.p, ray.d = refracted;
-          return true;
-        }
-      }
-      V3f reflected = reflect(ray.d, s.n);  // un-normalised d, unflipped hit.normal (Q14)
-      ray.o = s.p, ray.d = reflected;
-      return true;
-    }
-    case RTB_MAT_ISOTROPIC: {  // :165-168
-      *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
-      ray.o = s.p, ray.d = sample_unit_ball(rng);
-      return true;
-    }
-    default:  // RTB_MAT_DIFFUSE_LIGHT :144-146
-      return false;
+    ray.o = s.p, ray.d = dir;
+    return true;
   }
+  // Lambertian :49-53, Metal :76-86, Isotropic :165-168 share the ball sample and the albedo
+  V3f ball = sample_unit_ball(rnd.x, rnd.y, rnd.z);
+  V3f dir;
+  if (mat_type == RTB_MAT_LAMBERTIAN) {
+    dir = s.n + ball;  // target - p = normal + ball
+  } else if (mat_type == RTB_MAT_METAL) {
+    float inv_len = rsqrt_fast(dot(ray.d, ray.d));
+    dir = reflect(inv_len * ray.d, s.n);
+    if (mat_param > 0.0f) dir = madd(mat_param, ball, dir);
+    if (!(dot(dir, s.n) > 0.0f)) return false;
+  } else {
+    dir = ball;
+  }
+  *atten = texture_value<kStats>(sv, mat_tex, s.u, s.v, s.p, tc);
+  ray.o = s.p, ray.d = dir;
+  return true;
 }
 
 // ---- camera: src/camera.rs:53-67 ------------------------------------------------------------------
-// Draws (in stream order): jitter_u, jitter_v, lens_r, lens_phi, time.  The lens sample is the
-// uniform unit disk (r = sqrt(xi), phi = 2 pi xi) — same distribution as the rejection loop at
-// src/util.rs:15-24.  The lens draws are consumed even when lens_radius == 0 so the stream
-// layout is fixed; the time draw always happens, as upstream.
-__device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, PathRng& rng) {
-  float ju = rng.next(), jv = rng.next(), lr = rng.next(), lp = rng.next(), xt = rng.next();
-  float s = ((float)i + ju) / (float)nx;  // tests/test.rs:66-67
-  float t = ((float)j + jv) / (float)ny;
+// Draws: block 0 = (jitter_u, jitter_v, lens_r, lens_phi), block 1 = (time).  The lens sample is
+// the uniform unit disk (r = sqrt(xi), phi = 2 pi xi) — same distribution as the rejection loop
+// at src/util.rs:15-24; skipped iff lens_radius == 0 (src/camera.rs:54).  The time draw always
+// happens, as upstream (src/camera.rs:61).
+__device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, uint64_t seed, uint32_t pixel,
+                                           uint32_t sample) {
+  u4 b0 = philox4x32_10(u4{0u, pixel, sample, 0u}, (uint32_t)seed, (uint32_t)(seed >> 32));
+  u4 b1 = philox4x32_10(u4{1u, pixel, sample, 0u}, (uint32_t)seed, (uint32_t)(seed >> 32));
+  float ju = u01(b0.x), jv = u01(b0.y), lr = u01(b0.z), lp = u01(b0.w), xt = u01(b1.x);
+  float s = ((float)i + ju) * rcp_fast((float)nx);  // tests/test.rs:66-67
+  float t = ((float)j + jv) * rcp_fast((float)ny);
   V3f origin = mk(cam.origin[0], cam.origin[1], cam.origin[2]);
   if (cam.lens_radius != 0.0f) {
-    float r = cam.lens_radius * sqrtf(lr);
+    float r = cam.lens_radius * sqrt_fast(lr);
     float sn, cs;
     __sincosf((2.0f * lp - 1.0f) * CUDART_PI_F, &sn, &cs);
     float rx = r * cs, ry = r * sn;
@@ -602,7 +651,7 @@ __device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int
 
 __device__ __forceinline__ V3f background_color(int background, V3f d) {
   if (background == 1) {  // the gradient commented out at src/color.rs:18-20 (lit variant only)
-    float inv = rsqrtf(dot(d, d));
+    float inv = rsqrt_fast(dot(d, d));
     float t = 0.5f * (d.y * inv + 1.0f);
     return mk((1.0f - t) + t * 0.5f, (1.0f - t) + t * 0.7f, (1.0f - t) + t * 1.0f);
   }
