@@ -40,7 +40,7 @@ struct MegaParams {
   int max_depth;
   float t_min;
   int background;
-  int shade_threshold;  // lanes that must be waiting before the warp runs its shade phase
+  int k_node, k_leaf, k_shade;  // lanes a phase needs before the warp's scheduler runs it
   uint64_t seed;
 };
 
@@ -75,8 +75,8 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
 // nothing else is runnable), so each phase's code executes with a well-filled warp instead of
 // the ~7/32 lanes a naive per-thread path loop reaches on these scenes (profiles/).
 // Radiance sums go to a per-warp shared-memory tile and to the accumulation buffer once.
-template <bool kStats>
-__global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
+template <bool kStats, int kMinBlocks>
+__global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
                                                         unsigned long long* __restrict__ stats) {
   __shared__ float s_acc[8][96];
   __shared__ int s_next[8];
@@ -108,31 +108,54 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
   float inv_a = 1.0f;
   Hit best;
   best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
-  V3f thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
+  V3f thr = mk(1.f, 1.f, 1.f);
   int depth = 0, self_prim = -1, self_face = 0, pix_local = 0;
   uint32_t pixel = 0, sample = 0;
   int stack[RTB_STACK_DEPTH];
   int sp = 0;
   int cur = pool > 0 ? CUR_NEW : CUR_DONE;
 
+  // Scheduler: NODE runs (repeatedly) while >= k_node lanes sit at inner nodes; otherwise LEAF once
+  // >= k_leaf lanes hold a leaf, otherwise SHADE once >= k_shade lanes wait for it; when no
+  // phase reaches its threshold (drained pool, tiny scenes) the most populated one runs.
   for (;;) {
-    const unsigned m_node = __ballot_sync(0xffffffffu, cur >= 0);
+    unsigned m_node = __ballot_sync(0xffffffffu, cur >= 0);
+    while (__popc(m_node) >= P.k_node) {
+      // ------------------------------------------------------------------ NODE phase
+      if (cur >= 0) {
+        if (kStats) cnt.node_tests++;
+        int next, push;
+        const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+        if (nh == 2) stack[sp++] = push;
+        if (nh == 0) next = sp > 0 ? stack[--sp] : CUR_SHADE;
+        cur = next;
+      }
+      m_node = __ballot_sync(0xffffffffu, cur >= 0);
+    }
     const unsigned m_leaf = __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
     const unsigned m_shade = __ballot_sync(0xffffffffu, cur == CUR_SHADE || cur == CUR_NEW);
     if ((m_node | m_leaf | m_shade) == 0u) break;
     const int n_node = __popc(m_node), n_leaf = __popc(m_leaf), n_shade_l = __popc(m_shade);
+    int phase;  // 0 node, 1 leaf, 2 shade
+    if (n_leaf >= P.k_leaf) phase = 1;
+    else if (n_shade_l >= P.k_shade) phase = 2;
+    else phase = (n_node >= n_leaf && n_node >= n_shade_l) ? 0 : (n_leaf >= n_shade_l ? 1 : 2);
 
-    if (n_shade_l > 0 && (n_shade_l >= P.shade_threshold || (n_node | n_leaf) == 0)) {
+    if (phase == 2) {
       // ------------------------------------------------------------------ SHADE phase
       if (cur == CUR_SHADE || cur == CUR_NEW) {
         bool need_new = cur == CUR_NEW;
         if (!need_new) {
           // the segment's closest surface hit is in `best`; media may pre-empt it
           n_segments++;
+          // all draws of this bounce: ball / schlick (a,b,c) and the first two media (d,e)
+          const Rand5 rnd = rand5(P.seed, (uint32_t)depth, pixel, sample, RTB_RNG_BOUNCE);
           int medium = -1;
           if (sv.n_media > 0)
-            medium = sample_media<kStats>(sv, ray, P.t_min, &best.t, P.seed, pixel, sample, (uint32_t)depth, &cnt);
+            medium = sample_media<kStats>(sv, ray, P.t_min, &best.t, rnd.d, rnd.e, P.seed, pixel, sample, (uint32_t)depth,
+                                          &cnt);
           bool ended = true;
+          V3f rad = mk(0.f, 0.f, 0.f);  // radiance this hit adds: thr * emitted (or background)
           if (medium >= 0 || best.prim >= 0) {
             Surface s;
             if (medium >= 0) {  // src/medium.rs:44-51
@@ -148,9 +171,8 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
             const int4 m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
             if (kStats) n_shade[m.x]++;
             if (m.x == RTB_MAT_DIFFUSE_LIGHT)  // emitted, src/color.rs:8 (zero for every other material)
-              rad = rad + thr * texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
+              rad = thr * texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
             if (depth < P.max_depth) {  // src/color.rs:9
-              const Rand4 rnd = rand4(P.seed, (uint32_t)depth, pixel, sample, 1u);
               V3f atten;
               if (scatter<kStats>(sv, m.x, m.y, __int_as_float(m.z), s, ray, rnd, &atten, &tc)) {
                 thr = thr * atten;
@@ -159,17 +181,15 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
               }
             }
           } else {
-            rad = rad + thr * background_color(P.background, ray.d);  // miss, src/color.rs:17-22
+            rad = thr * background_color(P.background, ray.d);  // miss, src/color.rs:17-22
           }
-          if (ended) {
-            if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
-              float* a = &s_acc[wib][pix_local * 3];
-              atomicAdd(a, rad.x);
-              atomicAdd(a + 1, rad.y);
-              atomicAdd(a + 2, rad.z);
-            }
-            need_new = true;
+          if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
+            float* a = &s_acc[wib][pix_local * 3];
+            atomicAdd(a, rad.x);
+            atomicAdd(a + 1, rad.y);
+            atomicAdd(a + 2, rad.z);
           }
+          need_new = ended;
         }
         // lanes whose path ended take the next paths of the warp's pool, in lane order
         const unsigned m_need = __ballot_sync(m_shade, need_new);
@@ -186,7 +206,7 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
             const int i = x0 + lx, row = y0 + ly;
             pixel = (uint32_t)(row * P.nx + i);
             ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.seed, pixel, sample);
-            thr = mk(1.f, 1.f, 1.f), rad = mk(0.f, 0.f, 0.f);
+            thr = mk(1.f, 1.f, 1.f);
             depth = 0, self_prim = -1, self_face = 0;
           } else {
             cur = CUR_DONE;
@@ -200,9 +220,8 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
           cur = sv.root;
         }
       }
-    } else if (n_node >= n_leaf) {
-      // ------------------------------------------------------------------ NODE phase
-      if (cur >= 0) {
+    } else if (phase == 0) {
+      if (cur >= 0) {  // below-threshold NODE step
         if (kStats) cnt.node_tests++;
         int next, push;
         const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
@@ -214,9 +233,9 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
       // ------------------------------------------------------------------ LEAF phase
       if (cur < 0 && cur > CUR_DONE) {
         const unsigned code = ~(unsigned)cur;
-        const int pi = (int)(code >> 3);
-        int count = (int)(code & 7u);
-        if (count > 0) {
+        const int first = (int)(code >> 3), count = (int)(code & 7u);
+        for (int q = 0; q < count; ++q) {
+          const int pi = first + q;
           float t;
           int face, id;
           if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, P.t_min, best.t, pi == self_prim, self_face, &t,
@@ -224,10 +243,8 @@ __global__ void __launch_bounds__(256, 2) k_render_mega(SceneView sv, DCamera ca
               (t < best.t || id > best.id)) {
             best.t = t, best.prim = pi, best.face = face, best.id = id;
           }
-          --count;
-          cur -= 7;  // first + 1, count - 1
         }
-        if (count == 0) cur = sp > 0 ? stack[--sp] : CUR_SHADE;
+        cur = sp > 0 ? stack[--sp] : CUR_SHADE;
       }
     }
   }
@@ -425,14 +442,22 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
-    P.shade_threshold = o.reserved[0] > 0 ? o.reserved[0] : 12;
+    // tuning knobs (opts.reserved[0..3]); defaults from the sweep in profiles/r1_mega_sweep.txt
+    P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 8;
+    P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;
+    P.k_shade = o.reserved[2] > 0 ? o.reserved[2] : 8;
+    const int min_blocks = o.reserved[3] > 0 ? o.reserved[3] : 4;
     const long long warps = tiles * P.slices;
     const int block = 256;
     const long long blocks = (warps * 32 + block - 1) / block;
     if (o.collect_stats)
-      k_render_mega<true><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+      k_render_mega<true, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+    else if (min_blocks == 2)
+      k_render_mega<false, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+    else if (min_blocks == 4)
+      k_render_mega<false, 4><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
     else
-      k_render_mega<false><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+      k_render_mega<false, 3><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
     ++*launches;
   }
   CUDA_TRY(cudaGetLastError());
@@ -636,14 +661,12 @@ int rtb_primary_rays(const RtbCamera* c, int nx, int ny, int sidx, uint64_t seed
     ver[i] = 2.0 * half_height * v[i];
   }
   const double lens_radius = c->aperture / 2.0;
-  const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
   for (int row = 0; row < ny; ++row) {
     const int j = ny - 1 - row;
     for (int i = 0; i < nx; ++i) {
       const uint32_t pixel = (uint32_t)(row * nx + i);
-      u4 b0 = philox4x32_10(u4{0u, pixel, (uint32_t)sidx, 0u}, k0, k1);
-      u4 b1 = philox4x32_10(u4{1u, pixel, (uint32_t)sidx, 0u}, k0, k1);
-      double ju = u01(b0.x), jv = u01(b0.y), lr = u01(b0.z), lp = u01(b0.w), xt = u01(b1.x);
+      const Rand5 r5 = rand5(seed, 0u, pixel, (uint32_t)sidx, RTB_RNG_CAMERA);
+      double ju = r5.a, jv = r5.b, lr = r5.c, lp = r5.d, xt = r5.e;
       double sx = ((double)i + ju) / (double)nx, ty = ((double)j + jv) / (double)ny;
       double org[3] = {c->look_from[0], c->look_from[1], c->look_from[2]};
       if (lens_radius != 0.0) {

@@ -70,15 +70,8 @@ __device__ __forceinline__ float sin_reduced(float x) {
 // (jitter_u, jitter_v, lens_r, lens_phi), block 1 = (time,-,-,-); purpose 1: block = depth,
 // the scatter draws of that bounce (ball x3, schlick); purpose 2 + g: block = depth, the
 // free-flight draws of media 4g .. 4g+3 on that segment.
-struct Rand4 {
-  float x, y, z, w;
-};
-__device__ __forceinline__ float u01_open(uint32_t v) { return ((float)(v >> 8) + 0.5f) * (1.0f / 16777216.0f); }
-__device__ __forceinline__ Rand4 rand4(uint64_t seed, uint32_t block, uint32_t pixel, uint32_t sample, uint32_t purpose) {
-  u4 r = philox4x32_10(u4{block, pixel, sample, purpose}, (uint32_t)seed, (uint32_t)(seed >> 32));
-  // (k + 0.5) * 2^-24 lies strictly inside (0,1): no zero-length ball sample, no log(0)
-  return Rand4{u01_open(r.x), u01_open(r.y), u01_open(r.z), u01_open(r.w)};
-}
+// (Rand5 / rand5 live in philox.h: five 24-bit uniforms per Philox call, strictly inside (0,1),
+// so there is no zero-length ball sample and no log(0).)
 
 // uniform in the unit ball == the distribution of the rejection loop at src/util.rs:4-13,
 // sampled directly from 3 draws (no divergence)
@@ -433,21 +426,44 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
 // the reference's list scan (Q13).  Returns the index of the medium that scattered, or -1.
 template <bool kStats>
 __device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray, float t_min, float* t_closest,
-                                            uint64_t seed, uint32_t pixel, uint32_t sample, uint32_t depth, Counters* cnt) {
+                                            float xi0, float xi1, uint64_t seed, uint32_t pixel, uint32_t sample,
+                                            uint32_t depth, Counters* cnt) {
+  // xi0, xi1: the free-flight draws of media 0 and 1 (slots d, e of the bounce block); media
+  // 2.. take theirs from extra Philox blocks (purpose RTB_RNG_MEDIA + g), five at a time.
   int which = -1;
   const float a = dot(ray.d, ray.d);
   const float inv_a = rcp_fast(a);
   const float inv_len = rsqrt_fast(a);
   const float len = a * inv_len;
-  Rand4 rnd = rand4(seed, depth, pixel, sample, 2u);
+  Rand5 extra;
+  extra.a = extra.b = extra.c = extra.d = extra.e = 0.5f;
   for (int mi = 0; mi < sv.n_media; ++mi) {
     if (kStats) cnt->medium_tests++;
-    if (mi && (mi & 3) == 0) rnd = rand4(seed, depth, pixel, sample, 2u + (uint32_t)(mi >> 2));
-    const float xi = (mi & 3) == 0 ? rnd.x : ((mi & 3) == 1 ? rnd.y : ((mi & 3) == 2 ? rnd.z : rnd.w));
+    float xi = mi == 0 ? xi0 : xi1;
+    if (mi >= 2) {
+      const int q = (mi - 2) % 5;
+      if (q == 0) extra = rand5(seed, depth, pixel, sample, RTB_RNG_MEDIA + (uint32_t)((mi - 2) / 5));
+      xi = q == 0 ? extra.a : (q == 1 ? extra.b : (q == 2 ? extra.c : (q == 3 ? extra.d : extra.e)));
+    }
     const int4 raw = __ldg(reinterpret_cast<const int4*>(sv.media + mi));
     const int first = raw.x, count = raw.y;
     float t1 = 0.0f, t2 = 0.0f;
     bool ok = true;
+    const int4 C0 = ldg4i(&sv.bprims[first].c);
+    if (count == 1 && RTB_PRIM_TYPE(C0.x) <= DP_MOVING_SPHERE) {
+      // a sphere boundary: hit1 is the near root over (-MAX, MAX), hit2 the far root if it
+      // lies beyond hit1.t + 1e-4 (src/sphere.rs:45-62 called twice by src/medium.rs:30-31)
+      if (kStats) cnt->prim_tests += 2;
+      const float4 A = ldg4(&sv.bprims[first].a);
+      const float4 B = ldg4(&sv.bprims[first].b);
+      V3f oc = ray.o - sphere_center(A, B, C0, ray.time);
+      float tc = -dot(oc, ray.d) * inv_a;
+      V3f l = madd(tc, ray.d, oc);
+      float disc = fmaf(A.w, A.w, -dot(l, l));
+      float h = sqrt_fast(fmaxf(disc, 0.0f) * inv_a);
+      t1 = tc - h, t2 = tc + h;
+      ok = disc > 0.0f && t2 > t1 + 0.0001f;
+    } else {
 #pragma unroll 1
     for (int pass = 0; pass < 2 && ok; ++pass) {
       const float lo = pass == 0 ? -CUDART_INF_F : t1 + 0.0001f;
@@ -463,6 +479,7 @@ __device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray
       }
       ok = any;
       if (pass == 0) t1 = best; else t2 = best;
+    }
     }
     if (!ok) continue;
     if (t1 < t_min) t1 = t_min;
@@ -567,7 +584,7 @@ __device__ __forceinline__ V3f reflect(V3f v, V3f n) { return v - (2.0f * dot(v,
 // rnd: the four draws of this bounce (ball x3, schlick).
 template <bool kStats>
 __device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int mat_tex, float mat_param, const Surface& s,
-                                        RayF& ray, const Rand4& rnd, V3f* atten, TexCounters* tc) {
+                                        RayF& ray, const Rand5& rnd, V3f* atten, TexCounters* tc) {
   if (mat_type == RTB_MAT_DIFFUSE_LIGHT) return false;  // :144-146
   if (mat_type == RTB_MAT_DIELECTRIC) {                 // :106-126
     *atten = mk(1.0f, 1.0f, 1.0f);
@@ -596,13 +613,13 @@ __device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int m
       float m = 1.0f - cosine;
       float m2 = m * m;
       float reflect_prob = r0 + (1.0f - r0) * (m2 * m2 * m);
-      if (rnd.w >= reflect_prob) dir = ni_over_nt * (uv - dt * outward_normal) - sqrt_fast(discriminant) * outward_normal;
+      if (rnd.a >= reflect_prob) dir = ni_over_nt * (uv - dt * outward_normal) - sqrt_fast(discriminant) * outward_normal;
     }
     ray.o = s.p, ray.d = dir;
     return true;
   }
   // Lambertian :49-53, Metal :76-86, Isotropic :165-168 share the ball sample and the albedo
-  V3f ball = sample_unit_ball(rnd.x, rnd.y, rnd.z);
+  V3f ball = sample_unit_ball(rnd.a, rnd.b, rnd.c);
   V3f dir;
   if (mat_type == RTB_MAT_LAMBERTIAN) {
     dir = s.n + ball;  // target - p = normal + ball
@@ -626,9 +643,8 @@ __device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int m
 // happens, as upstream (src/camera.rs:61).
 __device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, uint64_t seed, uint32_t pixel,
                                            uint32_t sample) {
-  u4 b0 = philox4x32_10(u4{0u, pixel, sample, 0u}, (uint32_t)seed, (uint32_t)(seed >> 32));
-  u4 b1 = philox4x32_10(u4{1u, pixel, sample, 0u}, (uint32_t)seed, (uint32_t)(seed >> 32));
-  float ju = u01(b0.x), jv = u01(b0.y), lr = u01(b0.z), lp = u01(b0.w), xt = u01(b1.x);
+  const Rand5 r5 = rand5(seed, 0u, pixel, sample, RTB_RNG_CAMERA);
+  const float ju = r5.a, jv = r5.b, lr = r5.c, lp = r5.d, xt = r5.e;
   float s = ((float)i + ju) * rcp_fast((float)nx);  // tests/test.rs:66-67
   float t = ((float)j + jv) * rcp_fast((float)ny);
   V3f origin = mk(cam.origin[0], cam.origin[1], cam.origin[2]);
