@@ -149,6 +149,8 @@ int rtb_render(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns,
  * caller-zeroed) on `cuda_stream` (a cudaStream_t cast to void*, NULL = default stream)
  * without synchronising. */
 int rtb_scene_upload(rtb_scene*, int world, int device);
+/* bytes of flattened scene tables resident on the device after rtb_scene_upload (0 if none) */
+size_t rtb_scene_device_bytes(const rtb_scene*);
 int rtb_render_device(rtb_scene*, const RtbCamera*, int nx, int ny, int ns, const rtb_render_opts*,
                       float* d_sum_rgb, void* cuda_stream, rtb_stats*);
 /* tests/test.rs:71-78: /ns, sqrt, clamp[0,1], (255.99*c) as i32 — on device */

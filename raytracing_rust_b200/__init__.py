@@ -115,6 +115,7 @@ _sig("rtb_scene_prim_count", _i, _vp, _i)
 _sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
 _sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
 _sig("rtb_scene_upload", _i, _vp, _i, _i)
+_sig("rtb_scene_device_bytes", _sz, _vp)
 _sig("rtb_render_device", _i, _vp, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
 _sig("rtb_resolve_device", _i, _vp, _i, _i, _i, _vp, _vp)
 _sig("rtb_closest_hit", _i, _vp, _i, _vp, _sz, _d, _i, _vp, _vp)
@@ -290,6 +291,9 @@ class Scene:
 
     def upload(self, world, device=0):
         _h(lib.rtb_scene_upload(self._p, world, device), "scene_upload")
+
+    def device_bytes(self) -> int:
+        return lib.rtb_scene_device_bytes(self._p)
 
     def render_device(self, cam, nx, ny, ns, opts, d_sum_ptr: int, stream: int = 0, want_stats=False):
         st = Stats() if want_stats else None

@@ -492,6 +492,14 @@ void rtb_render_opts_default(rtb_render_opts* o) {
 
 int rtb_scene_upload(rtb_scene* s, int world, int device) { return ensure_uploaded(s, world, device, 0.0, 1.0); }
 
+size_t rtb_scene_device_bytes(const rtb_scene* s) {
+  if (!s || !s->dev) return 0;
+  const FlatScene& f = s->dev->flat;
+  return f.nodes.size() * sizeof(DNode) + (f.prims.size() + f.bprims.size()) * sizeof(DPrim) +
+         f.media.size() * sizeof(DMedium) + f.xforms.size() * sizeof(DXform) + f.mats.size() * sizeof(DMaterial) +
+         f.texs.size() * sizeof(DTexture) + f.perlin.size() * sizeof(DPerlin) + f.texels.size() * sizeof(uint32_t);
+}
+
 int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int ns, const rtb_render_opts* opts,
                       float* d_sum_rgb, void* cuda_stream, rtb_stats* stats) {
   if (!s || !camera || !opts || !d_sum_rgb || nx <= 0 || ny <= 0 || ns < 0)
