@@ -17,7 +17,8 @@ from pathlib import Path
 import numpy as np
 
 _HERE = Path(__file__).resolve().parent
-_LIB_PATH = _HERE / "librtb200.so"
+# RTB200_LIB: developer override used by tools/ to A/B experiment builds of the same library
+_LIB_PATH = Path(os.environ["RTB200_LIB"]).resolve() if os.environ.get("RTB200_LIB") else _HERE / "librtb200.so"
 ASSETS = _HERE.parent / "assets"
 
 if not _LIB_PATH.exists():

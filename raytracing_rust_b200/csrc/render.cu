@@ -18,6 +18,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -389,6 +391,9 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   CUDA_TRY(cudaGetDeviceProperties(&d->prop, device));
   s->dev = d;
   s->dev_world = world;
+  if (std::getenv("RTB200_DEBUG"))
+    std::fprintf(stderr, "[rtb200] uploaded: %zu nodes, %zu prims, %zu boundary prims, %zu media, %zu xforms, bvh depth %d\n",
+                 f.nodes.size(), f.prims.size(), f.bprims.size(), f.media.size(), f.xforms.size(), f.bvh_depth);
   return RTB_OK;
 }
 
