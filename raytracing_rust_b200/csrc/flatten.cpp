@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -241,7 +242,8 @@ struct Builder {
   const std::vector<Box3>& boxes;
   std::vector<int> order;  // primitive indices, permuted in place
   std::vector<BuildNode> nodes;
-  int max_leaf = 2;
+  int max_leaf = 1;  // single-primitive leaves measured best (profiles/r1_bvh_sweep.txt)
+  double c_trav = 1.0;  // cost of a node visit in units of one primitive test
   int depth_max = 0;
 
   int build(int first, int count, int depth) {
@@ -276,7 +278,7 @@ struct Builder {
       }
     }
     double parent_area = std::max(n.box.area(), 1e-300);
-    double split_cost = 1.0 + best / parent_area;  // traversal step + expected leaf tests
+    double split_cost = c_trav + best / parent_area;  // traversal step + expected leaf tests
     if (count <= max_leaf && split_cost >= (double)count) {
       nodes[idx].first = first, nodes[idx].count = count;
       return idx;
@@ -355,6 +357,8 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
     return RTB_OK;
   }
   Builder b{w.prim_boxes, {}, {}};
+  if (const char* e = std::getenv("RTB200_MAX_LEAF")) b.max_leaf = std::max(1, std::min(7, std::atoi(e)));
+  if (const char* e = std::getenv("RTB200_CTRAV")) b.c_trav = std::atof(e);
   b.order.resize(n);
   for (int i = 0; i < n; ++i) b.order[i] = i;
   int root = b.build(0, n, 0);

@@ -38,7 +38,8 @@ struct MegaParams {
   int sample_first;   // first sample index this launch renders
   int sample_step;    // distance between consecutive samples of this launch (GPU sharding stride)
   int sample_count;   // samples per pixel in this launch
-  int slices;         // warps per pixel tile (each takes every slices-th sample of the launch)
+  int slices;         // work items per pixel tile (each takes every slices-th sample of the launch)
+  int n_items;        // tiles * slices; warps draw items from a global counter until none is left
   int max_depth;
   float t_min;
   int background;
@@ -60,9 +61,28 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
 //   CUR_DONE                pool exhausted
 #define CUR_SHADE (-2147483647 - 1)
 #define CUR_NEW (-2147483647)
-#define CUR_DONE (-2147483646)
+#define CUR_DONE (-2147483645)
+#define CUR_WAIT (-2147483646)  // needs a path but the warp's current item is used up: waits for the next item
 
-// k_render_mega — one persistent warp per 8x4 pixel tile (x sample slice).
+// Adds one warp's finished accumulation tile to the image (one RED.global per non-zero
+// pixel-channel) and clears it.  All 32 lanes call it together.
+__device__ __forceinline__ void flush_tile(float* tile_acc, int4 info, int nx, int lane, float* __restrict__ accum) {
+  if (info.x >= 0) {
+    const int x0 = info.x, y0 = info.y, w_t = info.z & 255, n_pix = info.z >> 8;
+    for (int q = lane; q < n_pix * 3; q += 32) {
+      const float v = tile_acc[q];
+      if (v != 0.0f) {
+        const int pl = q / 3, c = q - pl * 3;
+        const int row = y0 + pl / w_t, i = x0 + pl % w_t;
+        atomicAdd(accum + 3ull * ((size_t)row * nx + i) + c, v);
+        tile_acc[q] = 0.0f;
+      }
+    }
+  }
+  __syncwarp();
+}
+
+// k_render_mega — persistent warps drawing (8x4 pixel tile x sample slice) work items.
 //
 // The reference runs   for pixel { for sample { color(ray) } }   with color() recursing up to 50
 // deep (tests/test.rs:62-70, src/color.rs:6-23).  Here a warp owns the pool of
@@ -79,24 +99,24 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
 // Radiance sums go to a per-warp shared-memory tile and to the accumulation buffer once.
 template <bool kStats, int kMinBlocks>
 __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
-                                                        unsigned long long* __restrict__ stats) {
-  __shared__ float s_acc[8][96];
-  __shared__ int s_next[8];
+                                                        unsigned long long* __restrict__ stats,
+                                                        unsigned int* __restrict__ work_counter) {
+  // Two accumulation tiles per warp: generation g of the warp's item sequence adds into s_acc[.][g & 1],
+  // so paths of the previous item may still be in flight while the next item's paths start.
+  __shared__ float s_acc[8][2][96];
+  __shared__ int s_next[8];      // next path id of the current item
+  __shared__ int4 s_item[8][2];  // work item behind each accumulation tile: (x0, y0, w_t | n_pix << 8, slice); x0 < 0: none
+  __shared__ int s_gen[8];       // which tile the current item uses
+  __shared__ int s_pool[8];      // paths in the current item
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const long long warp_global = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int tiles_x = (P.nx + 7) >> 3, tiles_y = (P.ny + 3) >> 2;
-  const long long tile = warp_global / P.slices;
-  const int slice = (int)(warp_global - tile * P.slices);
-  const int tx = (int)(tile % tiles_x), ty = (int)(tile / tiles_x);
-  const int x0 = tx * 8, y0 = ty * 4;  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
-  const int w_t = min(8, P.nx - x0), h_t = ty < tiles_y ? min(4, P.ny - y0) : 0;
-  const int n_pix = w_t * h_t;
-  const int my_count = slice < P.sample_count ? (P.sample_count - slice + P.slices - 1) / P.slices : 0;
-  const int pool = n_pix * my_count;  // paths this warp renders: id -> (pixel id % n_pix, sample id / n_pix)
+  const int tiles_x = (P.nx + 7) >> 3;
 
-  for (int q = lane; q < 96; q += 32) s_acc[wib][q] = 0.0f;
-  if (lane == 0) s_next[wib] = 0;
+  for (int q = lane; q < 192; q += 32) (&s_acc[wib][0][0])[q] = 0.0f;
+  if (lane == 0) {
+    s_next[wib] = 0, s_gen[wib] = 0, s_pool[wib] = 0;
+    s_item[wib][0] = make_int4(-1, 0, 0, 0), s_item[wib][1] = make_int4(-1, 0, 0, 0);
+  }
   __syncwarp();
 
   Counters cnt = {0, 0, 0};
@@ -115,7 +135,8 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
   uint32_t pixel = 0, sample = 0;
   int stack[RTB_STACK_DEPTH];
   int sp = 0;
-  int cur = pool > 0 ? CUR_NEW : CUR_DONE;
+  int cur = CUR_WAIT;
+  bool items_left = true;
 
   // Scheduler: NODE runs (repeatedly) while >= k_node lanes sit at inner nodes; otherwise LEAF once
   // >= k_leaf lanes hold a leaf, otherwise SHADE once >= k_shade lanes wait for it; when no
@@ -134,9 +155,42 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
       }
       m_node = __ballot_sync(0xffffffffu, cur >= 0);
     }
+    const unsigned m_wait = __ballot_sync(0xffffffffu, cur == CUR_WAIT);
+    if (m_wait != 0u) {
+      // the current item is used up.  Its tile partner (the previous item) must have drained
+      // before that tile can be flushed and reused for the next item.
+      const int g = s_gen[wib];
+      const bool alive = cur != CUR_DONE && cur != CUR_WAIT && cur != CUR_NEW;
+      const unsigned m_old = __ballot_sync(0xffffffffu, alive && (pix_local >> 5) != g);
+      if (m_old == 0u) {
+        const int g2 = g ^ 1;
+        flush_tile(s_acc[wib][g2], s_item[wib][g2], P.nx, lane, accum);
+        int item = P.n_items;
+        if (items_left) {
+          if (lane == 0) item = (int)atomicAdd(work_counter, 1u);
+          item = __shfl_sync(0xffffffffu, item, 0);
+        }
+        items_left = item < P.n_items;
+        __syncwarp();
+        if (lane == 0) {
+          int4 info = make_int4(-1, 0, 0, 0);
+          if (items_left) {
+            const int tile = item / P.slices, slice = item - tile * P.slices;
+            const int x0 = (tile % tiles_x) * 8, y0 = (tile / tiles_x) * 4;
+            const int w_t = min(8, P.nx - x0), n_pix = w_t * min(4, P.ny - y0);
+            const int my_count = slice < P.sample_count ? (P.sample_count - slice + P.slices - 1) / P.slices : 0;
+            info = make_int4(x0, y0, w_t | (n_pix << 8), slice);
+            s_gen[wib] = g2, s_pool[wib] = n_pix * my_count, s_next[wib] = 0;
+          }
+          s_item[wib][g2] = info;
+        }
+        __syncwarp();
+        if (cur == CUR_WAIT) cur = items_left ? CUR_NEW : CUR_DONE;
+      }
+    }
     const unsigned m_leaf = __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
     const unsigned m_shade = __ballot_sync(0xffffffffu, cur == CUR_SHADE || cur == CUR_NEW);
-    if ((m_node | m_leaf | m_shade) == 0u) break;
+    if ((m_node | m_leaf | m_shade) == 0u) break;  // (a waiting lane implies a live one, handled above)
     const int n_node = __popc(m_node), n_leaf = __popc(m_leaf), n_shade_l = __popc(m_shade);
     int phase;  // 0 node, 1 leaf, 2 shade
     if (n_leaf >= P.k_leaf) phase = 1;
@@ -186,35 +240,42 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
             rad = thr * background_color(P.background, ray.d);  // miss, src/color.rs:17-22
           }
           if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
-            float* a = &s_acc[wib][pix_local * 3];
+            float* a = &s_acc[wib][pix_local >> 5][(pix_local & 31) * 3];
             atomicAdd(a, rad.x);
             atomicAdd(a + 1, rad.y);
             atomicAdd(a + 2, rad.z);
           }
           need_new = ended;
         }
-        // lanes whose path ended take the next paths of the warp's pool, in lane order
+        // lanes whose path ended take the next paths of the warp's current item, in lane order
         const unsigned m_need = __ballot_sync(m_shade, need_new);
         if (need_new) {
-          const int base = s_next[wib];
+          const int base = s_next[wib], pool = s_pool[wib], g = s_gen[wib];
           const int id = base + __popc(m_need & lt_mask);
           __syncwarp(m_need);
-          if ((m_need & lt_mask) == 0u) s_next[wib] = base + __popc(m_need);
+          if ((m_need & lt_mask) == 0u) s_next[wib] = min(pool, base + __popc(m_need));
           if (id < pool) {
-            pix_local = id % n_pix;
-            const int k = slice + (id / n_pix) * P.slices;  // index in this launch's sample list
+            const int4 info = s_item[wib][g];
+            const int w_t = info.z & 255, n_pix = info.z >> 8;
+            int pl, ks, lx, ly;
+            if (info.z == (8 | (32 << 8))) {  // full 8x4 tile
+              pl = id & 31, ks = id >> 5, lx = pl & 7, ly = pl >> 3;
+            } else {
+              pl = id % n_pix, ks = id / n_pix, lx = pl % w_t, ly = pl / w_t;
+            }
+            pix_local = pl | (g << 5);
+            const int k = info.w + ks * P.slices;  // index in this launch's sample list
             sample = (uint32_t)(P.sample_first + k * P.sample_step);
-            const int lx = pix_local % w_t, ly = pix_local / w_t;
-            const int i = x0 + lx, row = y0 + ly;
+            const int i = info.x + lx, row = info.y + ly;  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
             pixel = (uint32_t)(row * P.nx + i);
             ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.seed, pixel, sample);
             thr = mk(1.f, 1.f, 1.f);
             depth = 0, self_prim = -1, self_face = 0;
           } else {
-            cur = CUR_DONE;
+            cur = CUR_WAIT;
           }
         }
-        if (cur != CUR_DONE) {  // start the next segment: world.hit(ray, t_min, MAX), src/color.rs:7
+        if (cur != CUR_WAIT) {  // start the next segment: world.hit(ray, t_min, MAX), src/color.rs:7
           ri = make_ray_inv(ray);
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
@@ -252,14 +313,8 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
   }
 
   __syncwarp();
-  for (int q = lane; q < n_pix * 3; q += 32) {
-    const float v = s_acc[wib][q];
-    if (v != 0.0f) {
-      const int pl = q / 3, c = q - pl * 3;
-      const int row = y0 + pl / w_t, i = x0 + pl % w_t;
-      atomicAdd(accum + 3ull * ((size_t)row * P.nx + i) + c, v);
-    }
-  }
+  flush_tile(s_acc[wib][0], s_item[wib][0], P.nx, lane, accum);
+  flush_tile(s_acc[wib][1], s_item[wib][1], P.nx, lane, accum);
   // counters: one atomic per warp
   unsigned long long v = warp_sum(n_segments);
   if (lane == 0 && v) atomicAdd(stats + 1, v);
@@ -388,6 +443,10 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   CUDA_TRY(cudaMalloc(&st, 32 * sizeof(unsigned long long)));
   d->allocs.push_back(st);
   d->d_stats = (unsigned long long*)st;
+  void* wk = nullptr;
+  CUDA_TRY(cudaMalloc(&wk, 64));
+  d->allocs.push_back(wk);
+  d->d_work = (unsigned int*)wk;
   CUDA_TRY(cudaGetDeviceProperties(&d->prop, device));
   s->dev = d;
   s->dev_world = world;
@@ -452,17 +511,22 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;
     P.k_shade = o.reserved[2] > 0 ? o.reserved[2] : 8;
     const int min_blocks = o.reserved[3] > 0 ? o.reserved[3] : 4;
-    const long long warps = tiles * P.slices;
+    const long long items = tiles * P.slices;
+    if (items > 0x7fffffffLL) return fail(RTB_ERR_INVALID, "render: image too large for one launch");
+    P.n_items = (int)items;
     const int block = 256;
-    const long long blocks = (warps * 32 + block - 1) / block;
+    // persistent grid: exactly the warps that are resident at once; they draw items until none is left
+    const long long blocks = std::min<long long>((items + 7) / 8, (long long)d->prop.multiProcessorCount * min_blocks);
+    unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
+    CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
     if (o.collect_stats)
-      k_render_mega<true, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+      k_render_mega<true, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
     else if (min_blocks == 2)
-      k_render_mega<false, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+      k_render_mega<false, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
     else if (min_blocks == 4)
-      k_render_mega<false, 4><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+      k_render_mega<false, 4><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
     else
-      k_render_mega<false, 3><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats);
+      k_render_mega<false, 3><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
     ++*launches;
   }
   CUDA_TRY(cudaGetLastError());

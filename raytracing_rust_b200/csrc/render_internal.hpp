@@ -19,6 +19,7 @@ struct DeviceScene {
   SceneView view{};  // device pointers
   std::vector<void*> allocs;
   unsigned long long* d_stats = nullptr;  // 32 counters
+  unsigned int* d_work = nullptr;         // work-item counter of the running megakernel launch
   cudaDeviceProp prop{};
   WavefrontState* wf = nullptr;
 };
