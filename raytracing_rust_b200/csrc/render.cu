@@ -130,9 +130,13 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
   float inv_a = 1.0f;
   Hit best;
   best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
-  V3f thr = mk(1.f, 1.f, 1.f);
-  int depth = 0, self_prim = -1, self_face = 0, pix_local = 0;
-  uint32_t pixel = 0, sample = 0;
+  // Path state only the SHADE phase touches is parked in shared memory (s_cold[word][thread],
+  // conflict-free) so the traversal loops do not carry it in registers or spill around it.
+  __shared__ float s_cold[7][256];
+#define COLD_F(w) s_cold[w][threadIdx.x]
+#define COLD_I(w) reinterpret_cast<int*>(s_cold[w])[threadIdx.x]
+  COLD_I(6) = 0;  // pix_local
+  int self_prim = -1, self_face = 0;
   int stack[RTB_STACK_DEPTH];
   int sp = 0;
   int cur = CUR_WAIT;
@@ -161,7 +165,7 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
       // before that tile can be flushed and reused for the next item.
       const int g = s_gen[wib];
       const bool alive = cur != CUR_DONE && cur != CUR_WAIT && cur != CUR_NEW;
-      const unsigned m_old = __ballot_sync(0xffffffffu, alive && (pix_local >> 5) != g);
+      const unsigned m_old = __ballot_sync(0xffffffffu, alive && (COLD_I(6) >> 5) != g);
       if (m_old == 0u) {
         const int g2 = g ^ 1;
         flush_tile(s_acc[wib][g2], s_item[wib][g2], P.nx, lane, accum);
@@ -201,6 +205,9 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
       // ------------------------------------------------------------------ SHADE phase
       if (cur == CUR_SHADE || cur == CUR_NEW) {
         bool need_new = cur == CUR_NEW;
+        V3f thr = mk(COLD_F(0), COLD_F(1), COLD_F(2));
+        uint32_t pixel = (uint32_t)COLD_I(3), sample = (uint32_t)COLD_I(4);
+        int depth = COLD_I(5), pix_local = COLD_I(6);
         if (!need_new) {
           // the segment's closest surface hit is in `best`; media may pre-empt it
           n_segments++;
@@ -276,6 +283,8 @@ __global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, D
           }
         }
         if (cur != CUR_WAIT) {  // start the next segment: world.hit(ray, t_min, MAX), src/color.rs:7
+          COLD_F(0) = thr.x, COLD_F(1) = thr.y, COLD_F(2) = thr.z;
+          COLD_I(3) = (int)pixel, COLD_I(4) = (int)sample, COLD_I(5) = depth, COLD_I(6) = pix_local;
           ri = make_ray_inv(ray);
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
@@ -507,10 +516,10 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
     // tuning knobs (opts.reserved[0..3]); defaults from the sweep in profiles/r1_mega_sweep.txt
-    P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 8;
+    P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 4;
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;
-    P.k_shade = o.reserved[2] > 0 ? o.reserved[2] : 8;
-    const int min_blocks = o.reserved[3] > 0 ? o.reserved[3] : 4;
+    P.k_shade = o.reserved[2] > 0 ? o.reserved[2] : 4;
+    const int min_blocks = o.reserved[3] > 0 ? o.reserved[3] : 3;
     const long long items = tiles * P.slices;
     if (items > 0x7fffffffLL) return fail(RTB_ERR_INVALID, "render: image too large for one launch");
     P.n_items = (int)items;
