@@ -97,8 +97,8 @@ __device__ __forceinline__ void flush_tile(float* tile_acc, int4 info, int nx, i
 // nothing else is runnable), so each phase's code executes with a well-filled warp instead of
 // the ~7/32 lanes a naive per-thread path loop reaches on these scenes (profiles/).
 // Radiance sums go to a per-warp shared-memory tile and to the accumulation buffer once.
-template <bool kStats, int kMinBlocks>
-__global__ void __launch_bounds__(256, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
+template <bool kStats, int kThreads, int kMinBlocks>
+__global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
                                                         unsigned long long* __restrict__ stats,
                                                         unsigned int* __restrict__ work_counter) {
   // Two accumulation tiles per warp: generation g of the warp's item sequence adds into s_acc[.][g & 1],
@@ -523,19 +523,28 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     const long long items = tiles * P.slices;
     if (items > 0x7fffffffLL) return fail(RTB_ERR_INVALID, "render: image too large for one launch");
     P.n_items = (int)items;
-    const int block = 256;
+    // occupancy point (threads per block, blocks per SM -> register cap): 2..4 = 256-thread blocks
+    // (125 / 80 / 64 registers), 5..7 = 128-thread blocks (102 / 85 / 73 registers)
+    const int block = min_blocks >= 5 ? 128 : 256;
+    const int wpb = block / 32;
     // persistent grid: exactly the warps that are resident at once; they draw items until none is left
-    const long long blocks = std::min<long long>((items + 7) / 8, (long long)d->prop.multiProcessorCount * min_blocks);
+    const long long blocks = std::min<long long>((items + wpb - 1) / wpb, (long long)d->prop.multiProcessorCount * min_blocks);
     unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
     CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
-    if (o.collect_stats)
-      k_render_mega<true, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
-    else if (min_blocks == 2)
-      k_render_mega<false, 2><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
-    else if (min_blocks == 4)
-      k_render_mega<false, 4><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
-    else
-      k_render_mega<false, 3><<<(unsigned)blocks, block, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);
+#define RTB_LAUNCH_MEGA(ST, TH, MB) \
+  k_render_mega<ST, TH, MB><<<(unsigned)blocks, TH, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc)
+    if (o.collect_stats) {
+      if (block == 256) RTB_LAUNCH_MEGA(true, 256, 2); else RTB_LAUNCH_MEGA(true, 128, 4);
+    } else {
+      switch (min_blocks) {
+        case 2: RTB_LAUNCH_MEGA(false, 256, 2); break;
+        case 4: RTB_LAUNCH_MEGA(false, 256, 4); break;
+        case 5: RTB_LAUNCH_MEGA(false, 128, 5); break;
+        case 6: RTB_LAUNCH_MEGA(false, 128, 6); break;
+        case 7: RTB_LAUNCH_MEGA(false, 128, 7); break;
+        default: RTB_LAUNCH_MEGA(false, 256, 3); break;
+      }
+    }
     ++*launches;
   }
   CUDA_TRY(cudaGetLastError());
