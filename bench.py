@@ -151,6 +151,8 @@ def run_reference(args):
 
 
 def run_gpu(args):
+    # stdout carries exactly one JSON line: NCCL's version / debug banner goes to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -168,7 +170,14 @@ def run_gpu(args):
 
     scene, w, cam = rtb.Scene.named(SCENE, NX, NY)
     scene.upload(w, local)
-    acc = torch.zeros(NY, NX, 3, dtype=torch.float32, device=dev)
+    reducer = None
+    if world > 1 and args.reduce == "p2p":
+        # accumulation buffers owned by librtb200 and exported to rank 0: the exchange step is the
+        # fused P2P reduce + resolve kernel (csrc/peer.cu) instead of NCCL reduce + resolve
+        reducer = D.PeerReducer(NX, NY, local)
+        acc = reducer.acc
+    else:
+        acc = torch.zeros(NY, NX, 3, dtype=torch.float32, device=dev)
     rgb8 = torch.empty(NY, NX, 3, dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
@@ -203,9 +212,12 @@ def run_gpu(args):
             step(k, opts)
             ev[k][1].record()
         ev[-1][0].record()
-        if world > 1:  # the path's one exchange step: sum-reduce of the accumulation buffers to rank 0
-            D.reduce_accumulators(acc, dst=0)
-        rtb.resolve_device(acc.data_ptr(), NX, NY, max(1, args.steps * ns_total), rgb8.data_ptr(), stream)
+        if reducer is not None:  # the path's one exchange step, fused with the resolve, over peer memory
+            reducer.reduce_resolve(max(1, args.steps * ns_total), rgb8, stream=stream)
+        else:
+            if world > 1:  # the exchange step: sum-reduce of the accumulation buffers to rank 0 (NCCL)
+                D.reduce_accumulators(acc, dst=0)
+            rtb.resolve_device(acc.data_ptr(), NX, NY, max(1, args.steps * ns_total), rgb8.data_ptr(), stream)
         ev[-1][1].record()
         torch.cuda.synchronize()
     if world > 1:
@@ -274,7 +286,9 @@ def run_gpu(args):
         "config": {"workload": f"{SCENE} as written (tests/test.rs:419-523), {NX}x{NY}, {spp} spp per step per GPU, max_depth 50, "
                                f"black background; 10k-spp image = {10000 // spp} steps; L2 flushed (256 MB write) between timed steps",
                    "pipeline": args.pipeline, "seconds_per_4k_10kspp_image": NX * NY * 10000 / (value * 1e6),
-                   "parallelism": f"spp-shard x{world}" + (" + NCCL reduce(sum) to rank 0" if world > 1 else "")},
+                   "parallelism": f"spp-shard x{world}" + ((" + fused P2P reduce+resolve on rank 0" if reducer is not None
+                                                             else " + NCCL reduce(sum) to rank 0") if world > 1 else ""),
+                   "exchange_ms": tail_ms},
         "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps + 1), "clocks": ck, "roofline": roofline,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_desc},
     }
@@ -289,6 +303,7 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reduce", default="nccl", choices=["nccl", "p2p"], help="N>1 exchange step: NCCL reduce + resolve, or the fused P2P kernel")
     ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--spp-per-step", type=int, default=SPP_PER_STEP)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

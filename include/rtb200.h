@@ -157,6 +157,26 @@ int rtb_render_device(rtb_scene*, const RtbCamera*, int nx, int ny, int ns, cons
 int rtb_resolve_device(const float* d_sum_rgb, int nx, int ny, int ns, uint8_t* d_rgb8,
                        void* cuda_stream);
 
+/* ---- multi-GPU exchange step over peer memory (csrc/peer.cu) ------------------------------
+ * The reference has no counterpart (single thread, tests/test.rs:64-70 keeps one accumulator per
+ * pixel); with samples sharded over G GPUs these calls combine the G partial sums.
+ *   rtb_device_alloc / _free : a zeroed accumulation buffer that is a whole CUDA allocation, so
+ *                              its base pointer can be exported to the other ranks' processes
+ *   rtb_peer_export          : cudaIpcGetMemHandle -> 64 opaque bytes to hand to the root rank
+ *   rtb_peer_open / _close   : map a peer's buffer into this process (P2P over NVLink)
+ *   rtb_reduce_resolve_device: ONE kernel on the root: sum of n_bufs buffers (own + peer-mapped,
+ *                              added in array order) -> tests/test.rs:71-78 quantisation into
+ *                              d_rgb8, and the f32 total into d_total if it is not NULL */
+#define RTB_IPC_HANDLE_BYTES 64
+#define RTB_MAX_PEER_BUFFERS 16
+int rtb_device_alloc(size_t bytes, int device, void** d_ptr);
+int rtb_device_free(void* d_ptr);
+int rtb_peer_export(const void* d_ptr, void* handle64);
+int rtb_peer_open(const void* handle64, int device, void** d_ptr);
+int rtb_peer_close(void* d_ptr);
+int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, int ny, int ns,
+                              float* d_total, uint8_t* d_rgb8, void* cuda_stream);
+
 /* Closest-hit query for the primitive-ID parity test: Hittable::hit(ray, t_min, f64::MAX)
  * (src/color.rs:7) with ConstantMedium objects skipped.  rays = n x {ox,oy,oz,dx,dy,dz,time}
  * (host, double); out_prim[i] = primitive ID or -1; out_t[i] = t (undefined on a miss). */

@@ -119,6 +119,12 @@ _sig("rtb_scene_upload", _i, _vp, _i, _i)
 _sig("rtb_scene_device_bytes", _sz, _vp)
 _sig("rtb_render_device", _i, _vp, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
 _sig("rtb_resolve_device", _i, _vp, _i, _i, _i, _vp, _vp)
+_sig("rtb_device_alloc", _i, _sz, _i, C.POINTER(C.c_void_p))
+_sig("rtb_device_free", _i, _vp)
+_sig("rtb_peer_export", _i, _vp, _vp)
+_sig("rtb_peer_open", _i, _vp, _i, C.POINTER(C.c_void_p))
+_sig("rtb_peer_close", _i, _vp)
+_sig("rtb_reduce_resolve_device", _i, C.POINTER(C.c_void_p), _i, _i, _i, _i, _vp, _vp, _vp)
 _sig("rtb_closest_hit", _i, _vp, _i, _vp, _sz, _d, _i, _vp, _vp)
 _sig("rtb_debug_texture_value", _i, _vp, _i, _i, _vp, _sz, _i, _vp)
 _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
@@ -322,6 +328,62 @@ class Scene:
 
 def resolve_device(d_sum_ptr: int, nx, ny, ns, d_rgb8_ptr: int, stream: int = 0):
     _h(lib.rtb_resolve_device(d_sum_ptr, nx, ny, ns, d_rgb8_ptr, stream), "resolve_device")
+
+
+IPC_HANDLE_BYTES = 64
+MAX_PEER_BUFFERS = 16
+
+
+class DeviceBuffer:
+    """A zeroed device allocation owned by librtb200 (rtb_device_alloc): a whole CUDA allocation,
+    so it can be exported to the other ranks (peer_handle) for the fused reduce + resolve.
+    `__cuda_array_interface__` lets torch / cupy view it without a copy."""
+
+    def __init__(self, shape, dtype=np.float32, device=0):
+        self.shape, self.dtype, self.device = tuple(int(x) for x in shape), np.dtype(dtype), device
+        self.nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        p = C.c_void_p()
+        _h(lib.rtb_device_alloc(self.nbytes, device, C.byref(p)), "device_alloc")
+        self.ptr = p.value
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": self.shape, "typestr": self.dtype.str, "data": (self.ptr, False), "version": 3, "strides": None}
+
+    def peer_handle(self) -> bytes:
+        h = C.create_string_buffer(IPC_HANDLE_BYTES)
+        _h(lib.rtb_peer_export(self.ptr, h), "peer_export")
+        return h.raw
+
+    def free(self):
+        if self.ptr:
+            _h(lib.rtb_device_free(self.ptr), "device_free")
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def peer_open(handle: bytes, device: int) -> int:
+    """Maps a peer rank's DeviceBuffer into this process; returns the device pointer."""
+    p = C.c_void_p()
+    _h(lib.rtb_peer_open(C.create_string_buffer(handle, IPC_HANDLE_BYTES), device, C.byref(p)), "peer_open")
+    return p.value
+
+
+def peer_close(ptr: int):
+    _h(lib.rtb_peer_close(ptr), "peer_close")
+
+
+def reduce_resolve_device(sum_ptrs, nx, ny, ns, d_rgb8_ptr: int, d_total_ptr: int = 0, stream: int = 0):
+    """One kernel: sum of the accumulation buffers in `sum_ptrs` (device pointers, own or
+    peer-mapped, added in list order) -> quantised rgb8 (and the f32 total if d_total_ptr)."""
+    arr = (C.c_void_p * len(sum_ptrs))(*sum_ptrs)
+    _h(lib.rtb_reduce_resolve_device(arr, len(sum_ptrs), nx, ny, ns, d_total_ptr or None, d_rgb8_ptr, stream or None),
+       "reduce_resolve_device")
 
 
 def primary_rays(cam, nx, ny, sample=0, seed=1) -> np.ndarray:

@@ -47,6 +47,61 @@ def reduce_accumulators(acc: torch.Tensor, dst: int = 0) -> torch.Tensor:
     return acc
 
 
+class PeerReducer:
+    """The exchange step as ONE kernel over peer memory instead of an NCCL reduce + resolve.
+
+    Every rank allocates its accumulation buffer through librtb200 (`rtb.DeviceBuffer`) and
+    exports it (CUDA IPC); the root maps the peers' buffers once.  `reduce_resolve` then
+      1. waits until every rank's render kernels finished (stream sync + barrier),
+      2. on the root, launches k_reduce_resolve (csrc/peer.cu): P2P loads of all G partial sums
+         over NVLink, added in rank order, quantised straight to rgb8 (tests/test.rs:71-78),
+      3. releases the peers (barrier) so they may clear / reuse their buffers.
+    Works on one node (NVLink / NVSwitch); `dist` only carries the 64-byte handles and barriers."""
+
+    def __init__(self, nx: int, ny: int, local_device: int, root: int = 0):
+        import raytracing_rust_b200 as rtb
+
+        self.rtb, self.nx, self.ny, self.device, self.root = rtb, nx, ny, local_device, root
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        if self.world > rtb.MAX_PEER_BUFFERS:
+            raise ValueError(f"PeerReducer supports up to {rtb.MAX_PEER_BUFFERS} ranks")
+        self.buf = rtb.DeviceBuffer((ny, nx, 3), "float32", local_device)
+        self.acc = torch.as_tensor(self.buf, device=torch.device("cuda", local_device))  # zero-copy view
+        handles = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(handles, self.buf.peer_handle())
+        self.ptrs, self._opened = [], []
+        if self.rank == root:
+            for r in range(self.world):
+                if r == self.rank:
+                    self.ptrs.append(self.buf.ptr)
+                else:
+                    p = rtb.peer_open(handles[r], local_device)
+                    self._opened.append(p)
+                    self.ptrs.append(p)
+        if self.world > 1:
+            dist.barrier()
+
+    def reduce_resolve(self, ns: int, rgb8: torch.Tensor, total: torch.Tensor | None = None, stream: int = 0):
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier()
+        if self.rank == self.root:
+            self.rtb.reduce_resolve_device(self.ptrs, self.nx, self.ny, ns, rgb8.data_ptr(),
+                                           total.data_ptr() if total is not None else 0, stream)
+            torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            dist.barrier()
+
+    def close(self):
+        for p in self._opened:
+            self.rtb.peer_close(p)
+        self._opened = []
+        del self.acc
+        self.buf.free()
+
+
 def render_sharded(scene, cam, nx, ny, ns, opts, acc: torch.Tensor, rank: int, world: int, stream: int = 0):
     """Adds this rank's share of the ns samples into `acc` (CUDA float32 [ny,nx,3], caller-zeroed)
     on the given CUDA stream, without synchronising.  The scene must be uploaded."""
