@@ -233,11 +233,16 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             }
             const int4 m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
             if (kStats) n_shade[m.x]++;
-            if (m.x == RTB_MAT_DIFFUSE_LIGHT)  // emitted, src/color.rs:8 (zero for every other material)
-              rad = thr * texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
+            // the material's one texture lookup: emitted colour of a DiffuseLight (src/color.rs:8, zero for
+            // every other material) or the albedo every scattering material but Dielectric multiplies in
+            V3f tex_rgb = mk(1.f, 1.f, 1.f);
+            if (m.x != RTB_MAT_DIELECTRIC && (m.x == RTB_MAT_DIFFUSE_LIGHT || depth < P.max_depth))
+              tex_rgb = texture_value<kStats>(sv, m.y, s.u, s.v, s.p, &tc);
+            if (m.x == RTB_MAT_DIFFUSE_LIGHT) rad = thr * tex_rgb;
             if (depth < P.max_depth) {  // src/color.rs:9
               V3f atten;
-              if (scatter<kStats>(sv, m.x, m.y, __int_as_float(m.z), s, ray, rnd, &atten, &tc)) {
+              if (scatter_dir(m.x, __int_as_float(m.z), s, ray, rnd)) {
+                atten = tex_rgb;
                 thr = thr * atten;
                 ++depth;
                 ended = false;

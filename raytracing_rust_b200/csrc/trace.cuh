@@ -636,6 +636,57 @@ __device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int m
   return true;
 }
 
+// Material::scatter without the albedo lookup (the caller evaluates the material's texture once
+// for both `emitted` and the attenuation): returns false when the path ends, else `ray` becomes
+// the scattered ray.  Same arithmetic as scatter() above.
+__device__ __forceinline__ bool scatter_dir(int mat_type, float mat_param, const Surface& s, RayF& ray, const Rand5& rnd) {
+  if (mat_type == RTB_MAT_DIFFUSE_LIGHT) return false;  // src/material.rs:144-146
+  if (mat_type == RTB_MAT_DIELECTRIC) {                 // :106-126
+    const float ref_idx = mat_param;
+    const float ddn = dot(ray.d, s.n);
+    const float inv_len = rsqrt_fast(dot(ray.d, ray.d));
+    V3f outward_normal;
+    float ni_over_nt, cosine;
+    if (ddn > 0.0f) {
+      cosine = ref_idx * ddn * inv_len;
+      outward_normal = -s.n;
+      ni_over_nt = ref_idx;
+    } else {
+      cosine = -ddn * inv_len;
+      outward_normal = s.n;
+      ni_over_nt = rcp_fast(ref_idx);
+    }
+    V3f uv = inv_len * ray.d;  // refract(), :13-23
+    float dt = dot(uv, outward_normal);
+    float discriminant = 1.0f - ni_over_nt * ni_over_nt * (1.0f - dt * dt);
+    V3f dir = reflect(ray.d, s.n);  // un-normalised d, unflipped hit.normal (Q14)
+    if (discriminant > 0.0f) {
+      float r0 = (1.0f - ref_idx) * rcp_fast(1.0f + ref_idx);  // schlick(), :25-28
+      r0 = r0 * r0;
+      float m = 1.0f - cosine;
+      float m2 = m * m;
+      float reflect_prob = r0 + (1.0f - r0) * (m2 * m2 * m);
+      if (rnd.a >= reflect_prob) dir = ni_over_nt * (uv - dt * outward_normal) - sqrt_fast(discriminant) * outward_normal;
+    }
+    ray.o = s.p, ray.d = dir;
+    return true;
+  }
+  V3f ball = sample_unit_ball(rnd.a, rnd.b, rnd.c);  // Lambertian :49-53, Metal :76-86, Isotropic :165-168
+  V3f dir;
+  if (mat_type == RTB_MAT_LAMBERTIAN) {
+    dir = s.n + ball;
+  } else if (mat_type == RTB_MAT_METAL) {
+    float inv_len = rsqrt_fast(dot(ray.d, ray.d));
+    dir = reflect(inv_len * ray.d, s.n);
+    if (mat_param > 0.0f) dir = madd(mat_param, ball, dir);
+    if (!(dot(dir, s.n) > 0.0f)) return false;
+  } else {
+    dir = ball;
+  }
+  ray.o = s.p, ray.d = dir;
+  return true;
+}
+
 // ---- camera: src/camera.rs:53-67 ------------------------------------------------------------------
 // Draws: block 0 = (jitter_u, jitter_v, lens_r, lens_phi), block 1 = (time).  The lens sample is
 // the uniform unit disk (r = sqrt(xi), phi = 2 pi xi) — same distribution as the rejection loop
