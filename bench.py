@@ -151,8 +151,11 @@ def run_reference(args):
 
 
 def run_gpu(args):
-    # stdout carries exactly one JSON line: NCCL's version / debug banner goes to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries exactly one JSON line: anything native libraries print on fd 1 while the job runs
+    # (NCCL's version banner) is sent to stderr, and the JSON line is written to the saved stdout
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -292,7 +295,8 @@ def run_gpu(args):
         "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps + 1), "clocks": ck, "roofline": roofline,
         "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_desc},
     }
-    print(json.dumps(line), flush=True)
+    sys.stdout.flush()
+    os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 
