@@ -105,6 +105,9 @@ int rtb_scene_named(rtb_scene*, const char* name, uint64_t seed, const uint8_t* 
 size_t rtb_scene_serialized_size(const rtb_scene*);
 int rtb_scene_serialize(const rtb_scene*, void* buf, size_t cap);
 rtb_scene* rtb_scene_deserialize(const void* buf, size_t len);
+/* the same bytes as a .rtscene file (the format host, oracle and GPU library share) */
+int rtb_scene_save(const rtb_scene*, const char* path);
+rtb_scene* rtb_scene_load(const char* path);
 /* number of leaf-primitive IDs under `world` (depth-first insertion order; a Cube owns 6,
  * in the order of src/cube.rs:21-74) */
 int rtb_scene_prim_count(rtb_scene*, int world);
@@ -143,6 +146,18 @@ void rtb_render_opts_default(rtb_render_opts*);
  *                 (only meaningful when the call renders all ns samples) */
 int rtb_render(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns,
                const rtb_render_opts*, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
+
+/* create_image in chunks of `chunk_spp` samples with real progress reporting (in place of the
+ * reference's dead src/progressbar.rs and the start/end lines of src/logger.rs): after every chunk
+ * `cb(user, samples_done, samples_total, rgb8_or_NULL, mpaths_per_s, eta_seconds)` is called; every
+ * `preview_every`-th chunk (0 = never) rgb8 is the host image so far, 3*nx*ny bytes valid during
+ * the call.  A non-zero return stops the render; the outputs then hold the mean of the
+ * *samples_done samples rendered.  Single-GPU call (sample_begin/stride must be 0/1). */
+typedef int (*rtb_progress_fn)(void* user, int samples_done, int samples_total, const uint8_t* rgb8,
+                               double mpaths_per_s, double eta_seconds);
+int rtb_render_progressive(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns,
+                           const rtb_render_opts*, int chunk_spp, int preview_every, rtb_progress_fn cb,
+                           void* user, float* out_sum_rgb, uint8_t* out_rgb8, int* samples_done);
 
 /* Device-resident variant for multi-GPU and benchmarking: the scene is uploaded once
  * (rtb_scene_upload), samples are ADDED into d_sum_rgb (device pointer, 3*nx*ny floats,
@@ -196,6 +211,11 @@ int rtb_debug_texture_value(rtb_scene*, int world, int tex, const double* uvp, s
 /* P3 text exactly as tests/test.rs:59,79: "P3\n{nx} {ny}\n255\n" + "{r} {g} {b}\n" per pixel.
  * Returns the byte count (excluding NUL); writes at most cap bytes. */
 size_t rtb_ppm_p3(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap);
+/* Binary PPM (P6) of the same image: "P6\n{nx} {ny}\n255\n" + 3*nx*ny raw bytes. */
+size_t rtb_ppm_p6(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap);
+/* File::create(path) + write!(file, "{}", create_image(..)) of the #[test] wrappers
+ * (tests/test.rs:536,557): binary == 0 writes the reference's P3 text, else P6. */
+int rtb_image_write_ppm(const char* path, const uint8_t* rgb8, int nx, int ny, int binary);
 
 #ifdef __cplusplus
 }

@@ -115,6 +115,9 @@ _sig("rtb_scene_deserialize", _vp, _vp, _sz)
 _sig("rtb_scene_prim_count", _i, _vp, _i)
 _sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
 _sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
+PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_double, C.c_double)
+_sig("rtb_render_progressive", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _i, _i, PROGRESS_FN, _vp,
+     _vp, _vp, C.POINTER(C.c_int))
 _sig("rtb_scene_upload", _i, _vp, _i, _i)
 _sig("rtb_scene_device_bytes", _sz, _vp)
 _sig("rtb_render_device", _i, _vp, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
@@ -129,6 +132,10 @@ _sig("rtb_closest_hit", _i, _vp, _i, _vp, _sz, _d, _i, _vp, _vp)
 _sig("rtb_debug_texture_value", _i, _vp, _i, _i, _vp, _sz, _i, _vp)
 _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
 _sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
+_sig("rtb_ppm_p6", _sz, _vp, _i, _i, _vp, _sz)
+_sig("rtb_image_write_ppm", _i, C.c_char_p, _vp, _i, _i, _i)
+_sig("rtb_scene_save", _i, _vp, C.c_char_p)
+_sig("rtb_scene_load", _vp, C.c_char_p)
 
 
 class RtbError(RuntimeError):
@@ -280,6 +287,17 @@ class Scene:
             raise RtbError(-1, "scene_deserialize")
         return cls(_ptr=p)
 
+    def save(self, path):
+        """Writes the scene as a .rtscene file (include/rtb_scene_format.h)."""
+        _h(lib.rtb_scene_save(self._p, str(path).encode()), "scene_save")
+
+    @classmethod
+    def load(cls, path):
+        p = lib.rtb_scene_load(str(path).encode())
+        if not p:
+            raise RtbError(-1, "scene_load")
+        return cls(_ptr=p)
+
     def prim_count(self, world):
         return _h(lib.rtb_scene_prim_count(self._p, world), "scene_prim_count")
 
@@ -295,6 +313,26 @@ class Scene:
                           out_sum.ctypes.data if want_sum else None, out_rgb8.ctypes.data if want_rgb8 else None,
                           C.byref(st) if want_stats else None), "render")
         return out_sum, out_rgb8, (st.as_dict() if want_stats else None)
+
+    def render_progressive(self, world, cam, nx, ny, ns, chunk_spp, on_progress=None, preview_every=0, opts=None, want_sum=False):
+        """create_image in chunks with real progress (rtb_render_progressive).  on_progress(done, total,
+        preview rgb8 [ny,nx,3] or None, mpaths_per_s, eta_s) -> truthy to stop.  Returns (sum or None, rgb8, done)."""
+        o = opts if opts is not None else default_opts()
+        out_sum = np.empty((ny, nx, 3), np.float32) if want_sum else None
+        out_rgb8 = np.empty((ny, nx, 3), np.uint8)
+        done = C.c_int(0)
+
+        def _cb(_user, d, total, img, rate, eta):
+            if on_progress is None:
+                return 0
+            prev = np.ctypeslib.as_array(img, shape=(ny, nx, 3)).copy() if img else None
+            return 1 if on_progress(d, total, prev, rate, eta) else 0
+
+        cb = PROGRESS_FN(_cb)
+        _h(lib.rtb_render_progressive(self._p, world, C.byref(cam), nx, ny, ns, C.byref(o), chunk_spp, preview_every, cb, None,
+                                      out_sum.ctypes.data if want_sum else None, out_rgb8.ctypes.data, C.byref(done)),
+           "render_progressive")
+        return out_sum, out_rgb8, done.value
 
     def upload(self, world, device=0):
         _h(lib.rtb_scene_upload(self._p, world, device), "scene_upload")
@@ -399,6 +437,21 @@ def ppm_p3(rgb8: np.ndarray) -> bytes:
     buf = C.create_string_buffer(n + 1)
     lib.rtb_ppm_p3(a.ctypes.data, nx, ny, buf, n + 1)
     return buf.raw[:n]
+
+
+def ppm_p6(rgb8: np.ndarray) -> bytes:
+    a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    ny, nx = a.shape[0], a.shape[1]
+    n = lib.rtb_ppm_p6(a.ctypes.data, nx, ny, None, 0)
+    buf = C.create_string_buffer(n)
+    lib.rtb_ppm_p6(a.ctypes.data, nx, ny, buf, n)
+    return buf.raw[:n]
+
+
+def write_ppm(path, rgb8: np.ndarray, binary=False):
+    """File::create + write! of the reference's #[test] wrappers (tests/test.rs:536,557); P3 text or P6."""
+    a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    _h(lib.rtb_image_write_ppm(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0], int(bool(binary))), "image_write_ppm")
 
 
 def create_image(ny, nx, ns, cam, scene: Scene, world: int, opts=None) -> bytes:

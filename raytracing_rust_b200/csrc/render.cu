@@ -689,6 +689,80 @@ int rtb_render(rtb_scene* s, int world, const RtbCamera* camera, int nx, int ny,
   return RTB_OK;
 }
 
+// Progressive create_image: the reference builds the whole image silently (its progress bar is
+// dead code that sleeps, src/progressbar.rs:6-58, and the logger only brackets the call,
+// tests/test.rs:809,837).  Here the sample loop runs in chunks; after every chunk the callback
+// sees real progress (samples done, measured Mpaths/s, ETA) and, every `preview_every` chunks,
+// the image so far (mean of the samples done, reference quantisation).
+int rtb_render_progressive(rtb_scene* s, int world, const RtbCamera* camera, int nx, int ny, int ns, const rtb_render_opts* opts,
+                           int chunk_spp, int preview_every, rtb_progress_fn cb, void* user, float* out_sum_rgb,
+                           uint8_t* out_rgb8, int* samples_done) {
+  if (!s || !camera || nx <= 0 || ny <= 0 || ns <= 0 || chunk_spp <= 0)
+    return fail(RTB_ERR_INVALID, "render_progressive: bad argument");
+  rtb_render_opts o;
+  if (opts) o = *opts; else rtb_render_opts_default(&o);
+  if (o.sample_begin != 0 || o.sample_stride > 1)
+    return fail(RTB_ERR_INVALID, "render_progressive: sample sharding is the caller's loop (use rtb_render_device)");
+  int rc = ensure_uploaded(s, world, o.device, std::min(camera->time0, camera->time1), std::max(camera->time0, camera->time1));
+  if (rc != RTB_OK) return rc;
+  CUDA_TRY(cudaSetDevice(o.device));
+  const size_t n = (size_t)3 * nx * ny;
+  float* d_sum = nullptr;
+  uint8_t* d_rgb8 = nullptr;
+  CUDA_TRY(cudaMalloc(&d_sum, n * sizeof(float)));
+  if (cudaMalloc(&d_rgb8, n) != cudaSuccess) {
+    cudaFree(d_sum);
+    return fail(RTB_ERR_CUDA, "render_progressive: out of device memory");
+  }
+  std::vector<uint8_t> preview(cb && preview_every > 0 ? n : 0);
+  auto finish = [&](int code) {
+    cudaFree(d_sum);
+    cudaFree(d_rgb8);
+    return code;
+  };
+  if (cudaMemset(d_sum, 0, n * sizeof(float)) != cudaSuccess) return finish(fail(RTB_ERR_CUDA, "memset"));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  int done = 0, chunks = 0;
+  double gpu_s = 0.0;
+  bool stop = false;
+  while (done < ns && !stop) {
+    const int upto = std::min(ns, done + chunk_spp);
+    o.sample_begin = done, o.sample_stride = 1;
+    cudaEventRecord(e0, 0);
+    rc = rtb_render_device(s, camera, nx, ny, upto, &o, d_sum, nullptr, nullptr);  // samples [done, upto)
+    if (rc != RTB_OK) break;
+    cudaEventRecord(e1, 0);
+    if (cudaEventSynchronize(e1) != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "render_progressive: kernel failed"); break; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    gpu_s += ms * 1e-3;
+    done = upto, ++chunks;
+    if (cb) {
+      const uint8_t* img = nullptr;
+      if (preview_every > 0 && (chunks % preview_every == 0 || done == ns)) {
+        rc = rtb_resolve_device(d_sum, nx, ny, done, d_rgb8, nullptr);
+        if (rc != RTB_OK) break;
+        if (cudaMemcpy(preview.data(), d_rgb8, n, cudaMemcpyDeviceToHost) != cudaSuccess) { rc = fail(RTB_ERR_CUDA, "preview copy"); break; }
+        img = preview.data();
+      }
+      const double rate = (double)nx * ny * done / std::max(gpu_s, 1e-9);
+      stop = cb(user, done, ns, img, rate * 1e-6, (double)nx * ny * (ns - done) / rate) != 0;
+    }
+  }
+  cudaEventDestroy(e0), cudaEventDestroy(e1);
+  if (rc != RTB_OK) return finish(rc);
+  if (samples_done) *samples_done = done;
+  if (out_rgb8) {
+    rc = rtb_resolve_device(d_sum, nx, ny, done, d_rgb8, nullptr);
+    if (rc != RTB_OK) return finish(rc);
+    if (cudaMemcpy(out_rgb8, d_rgb8, n, cudaMemcpyDeviceToHost) != cudaSuccess) return finish(fail(RTB_ERR_CUDA, "copy rgb8"));
+  }
+  if (out_sum_rgb && cudaMemcpy(out_sum_rgb, d_sum, n * sizeof(float), cudaMemcpyDeviceToHost) != cudaSuccess)
+    return finish(fail(RTB_ERR_CUDA, "copy sums"));
+  return finish(RTB_OK);
+}
+
 int rtb_closest_hit(rtb_scene* s, int world, const double* rays, size_t n, double t_min, int device, int32_t* out_prim,
                     float* out_t) {
   if (!s || (n && (!rays || !out_prim))) return fail(RTB_ERR_INVALID, "closest_hit: bad argument");

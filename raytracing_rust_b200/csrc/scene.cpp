@@ -3,8 +3,11 @@
 // here.  The CUDA flattener (flatten.cpp) and the CPU oracle both consume these records.
 #include "scene.hpp"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstring>
+#include <vector>
 
 namespace rtb {
 
@@ -420,6 +423,58 @@ size_t rtb_ppm_p3(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap) {
     if (n < cap) out[n] = 0;
   }
   return s.size();
+}
+
+size_t rtb_ppm_p6(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap) {
+  // binary sibling of the P3 text above: same header fields, raw bytes, rows top to bottom
+  std::string hdr = "P6\n" + std::to_string(nx) + " " + std::to_string(ny) + "\n255\n";
+  const size_t body = (size_t)3 * nx * ny, total = hdr.size() + body;
+  if (out && cap) {
+    size_t n = hdr.size() < cap ? hdr.size() : cap;
+    std::memcpy(out, hdr.data(), n);
+    if (cap > hdr.size()) std::memcpy(out + hdr.size(), rgb8, std::min(body, cap - hdr.size()));
+  }
+  return total;
+}
+
+int rtb_image_write_ppm(const char* path, const uint8_t* rgb8, int nx, int ny, int binary) {
+  // what the #[test] wrappers do with create_image's String (tests/test.rs:536,557: File::create + write!)
+  if (!path || !rgb8 || nx <= 0 || ny <= 0) return fail(RTB_ERR_INVALID, "image_write_ppm: bad argument");
+  const size_t n = binary ? rtb_ppm_p6(rgb8, nx, ny, nullptr, 0) : rtb_ppm_p3(rgb8, nx, ny, nullptr, 0);
+  std::vector<char> buf(n + 1);
+  if (binary) rtb_ppm_p6(rgb8, nx, ny, buf.data(), buf.size()); else rtb_ppm_p3(rgb8, nx, ny, buf.data(), buf.size());
+  FILE* f = std::fopen(path, "wb");
+  if (!f) return fail(RTB_ERR_INVALID, std::string("image_write_ppm: cannot create ") + path);
+  const size_t w = std::fwrite(buf.data(), 1, n, f);
+  if (std::fclose(f) != 0 || w != n) return fail(RTB_ERR_INVALID, std::string("image_write_ppm: short write to ") + path);
+  return RTB_OK;
+}
+
+int rtb_scene_save(const rtb_scene* s, const char* path) {
+  CHECK_SCENE(s);
+  if (!path) return fail(RTB_ERR_INVALID, "scene_save: null path");
+  std::vector<uint8_t> buf(rtb_scene_serialized_size(s));
+  int rc = rtb_scene_serialize(s, buf.data(), buf.size());
+  if (rc != RTB_OK) return rc;
+  FILE* f = std::fopen(path, "wb");
+  if (!f) return fail(RTB_ERR_INVALID, std::string("scene_save: cannot create ") + path);
+  const size_t w = std::fwrite(buf.data(), 1, buf.size(), f);
+  if (std::fclose(f) != 0 || w != buf.size()) return fail(RTB_ERR_INVALID, std::string("scene_save: short write to ") + path);
+  return RTB_OK;
+}
+
+rtb_scene* rtb_scene_load(const char* path) {
+  FILE* f = path ? std::fopen(path, "rb") : nullptr;
+  if (!f) {
+    rtb::set_error(std::string("scene_load: cannot open ") + (path ? path : "(null)"));
+    return nullptr;
+  }
+  std::vector<uint8_t> buf;
+  uint8_t chunk[1 << 16];
+  size_t n;
+  while ((n = std::fread(chunk, 1, sizeof chunk, f)) > 0) buf.insert(buf.end(), chunk, chunk + n);
+  std::fclose(f);
+  return rtb_scene_deserialize(buf.data(), buf.size());
 }
 
 }  // extern "C"

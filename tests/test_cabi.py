@@ -107,6 +107,33 @@ def test_ppm_p3_text_matches_reference_format(rtb):
     assert rtb.ppm_p3(img) == b"P3\n2 2\n255\n0 1 2\n10 99 100\n255 254 7\n0 0 0\n"
 
 
+def test_ppm_p6_and_file_writers(rtb, tmp_path):
+    img = np.array([[[0, 1, 2], [10, 99, 100]], [[255, 254, 7], [0, 0, 0]]], np.uint8)
+    assert rtb.ppm_p6(img) == b"P6\n2 2\n255\n" + img.tobytes()
+    rtb.write_ppm(tmp_path / "a.ppm", img)
+    assert (tmp_path / "a.ppm").read_bytes() == rtb.ppm_p3(img)
+    rtb.write_ppm(tmp_path / "b.ppm", img, binary=True)
+    assert (tmp_path / "b.ppm").read_bytes() == rtb.ppm_p6(img)
+    with pytest.raises(rtb.RtbError):  # File::create(..).expect("REASON") upstream (tests/test.rs:536)
+        rtb.write_ppm(tmp_path / "no_such_dir" / "c.ppm", img)
+    # the reference's committed all-black 800x800 renders are exactly this P3 text of a zero image
+    black = rtb.ppm_p3(np.zeros((800, 800, 3), np.uint8))
+    assert len(black) == 3_840_015 and black.startswith(b"P3\n800 800\n255\n0 0 0\n")
+
+
+def test_rtscene_file_roundtrip(rtb, tmp_path):
+    s, w, _ = rtb.Scene.named("final_scene", 32, 32)
+    s.save(tmp_path / "final.rtscene")
+    assert (tmp_path / "final.rtscene").read_bytes() == s.serialize()
+    s2 = rtb.Scene.load(tmp_path / "final.rtscene")
+    assert s2.serialize() == s.serialize() and s2.prim_count(w) == s.prim_count(w)
+    with pytest.raises(rtb.RtbError):
+        rtb.Scene.load(tmp_path / "missing.rtscene")
+    (tmp_path / "bad.rtscene").write_bytes(b"not a scene")
+    with pytest.raises(rtb.RtbError):
+        rtb.Scene.load(tmp_path / "bad.rtscene")
+
+
 def test_no_device_is_a_loud_error(rtb):
     if rtb.device_count() > 0:
         pytest.skip("a GPU is present")

@@ -243,3 +243,24 @@ def test_wavefront_small_capacity_and_sharding(rtb):
     b, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=9, pipeline=rtb.PIPE_MEGAKERNEL, sample_begin=1,
                                                            sample_stride=3), want_rgb8=False)
     _assert_same_estimate(a, b)
+
+
+def test_progressive_render_equals_one_shot_and_reports_progress(rtb):
+    # chunks of the sample loop add up to the one-shot image (counter-based RNG: same samples), the callback
+    # sees monotone progress, previews when asked, and a truthy return stops the render early
+    nx, ny, ns = 96, 64, 24
+    s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
+    ref_sum, ref8, _ = s.render(w, cam, nx, ny, ns)
+    seen = []
+    g_sum, g8, done = s.render_progressive(w, cam, nx, ny, ns, 5, lambda d, t, img, rate, eta: seen.append((d, t, img is not None, rate, eta)) and False,
+                                           preview_every=2, want_sum=True)
+    assert done == ns and [x[0] for x in seen] == [5, 10, 15, 20, 24] and all(x[1] == ns for x in seen)
+    assert [x[2] for x in seen] == [False, True, False, True, True] and all(x[3] > 0 for x in seen) and seen[-1][4] == 0.0
+    np.testing.assert_allclose(g_sum, ref_sum, rtol=1e-5, atol=1e-5)
+    assert np.abs(g8.astype(int) - ref8.astype(int)).max() <= 1
+    _, g8b, done = s.render_progressive(w, cam, nx, ny, ns, 8, lambda d, t, img, rate, eta: d >= 8)
+    assert done == 8
+    part_sum, part8, _ = s.render(w, cam, nx, ny, 8)
+    assert np.abs(g8b.astype(int) - part8.astype(int)).max() <= 1
+    with pytest.raises(rtb.RtbError):
+        s.render_progressive(w, cam, nx, ny, ns, 0)
