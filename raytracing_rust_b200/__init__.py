@@ -31,7 +31,7 @@ lib = C.CDLL(str(_LIB_PATH))
 PLANE_YZ, PLANE_ZX, PLANE_XY = 0, 1, 2
 AXIS_X, AXIS_Y, AXIS_Z = 0, 1, 2
 BG_BLACK, BG_SKY = 0, 1
-PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT = 0, 1, 2
+PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_POOL = 0, 1, 2, 3
 
 NAMED_SCENES = (
     "random_scene", "two_spheres", "two_perlin_sphere", "earth", "simple_light",

@@ -615,8 +615,11 @@ int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int
   }
   int pipe = opts->pipeline;
   if (pipe == RTB_PIPE_AUTO) pipe = RTB_PIPE_MEGAKERNEL;
+  if (pipe == RTB_PIPE_POOL && !pool_supports(d)) pipe = RTB_PIPE_MEGAKERNEL;  // BVH deeper than the pool's stack
   if (pipe == RTB_PIPE_WAVEFRONT)
     rc = launch_wavefront(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
+  else if (pipe == RTB_PIPE_POOL)
+    rc = launch_pool(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
   else
     rc = launch_mega(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
   if (rc != RTB_OK) return rc;

@@ -26,6 +26,19 @@ struct DeviceScene {
 
 int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi);
 void make_device_camera(const RtbCamera& c, DCamera* out);
+// pool.cu: path pool in shared memory (RTB_PIPE_POOL); needs bvh depth < RTB_POOL_STACK
+#ifndef RTB_POOL_ROWS
+#define RTB_POOL_ROWS 32
+#endif
+#ifndef RTB_POOL_THREADS
+#define RTB_POOL_THREADS 768
+#endif
+#ifndef RTB_POOL_STACK
+#define RTB_POOL_STACK 16
+#endif
+bool pool_supports(const DeviceScene* d);
+int launch_pool(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
+                cudaStream_t stream, uint64_t* launches);
 int launch_wavefront(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
                      cudaStream_t stream, uint64_t* launches);
 

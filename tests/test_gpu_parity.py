@@ -245,6 +245,37 @@ def test_wavefront_small_capacity_and_sharding(rtb):
     _assert_same_estimate(a, b)
 
 
+# ---- 8. the shared-memory path pool (RTB_PIPE_POOL) computes the same estimator as the megakernel --------
+@pytest.mark.parametrize("name,bg,nx,ny", [("cornell_box", 0, 96, 64), ("final_scene_lit", 0, 96, 64), ("random_scene", 1, 96, 64),
+                                           ("cornell_smoke_book", 0, 96, 64), ("two_perlin_sphere", 1, 96, 64),
+                                           ("earth", 1, 37, 19), ("simple_light", 0, 250, 130)])
+def test_pool_equals_megakernel(rtb, name, bg, nx, ny):
+    # same counter-based draws, same device functions: only who runs which path when differs (ragged sizes too)
+    ns = 24
+    s, w, cam = rtb.Scene.named(name, nx, ny)
+    a, _, sa = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, pipeline=rtb.PIPE_MEGAKERNEL),
+                        want_rgb8=False, want_stats=True)
+    b, _, sb = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, pipeline=rtb.PIPE_POOL),
+                        want_rgb8=False, want_stats=True)
+    assert sa["segments"] == sb["segments"] and sb["paths"] == nx * ny * ns
+    _assert_same_estimate(a, b)
+
+
+def test_pool_sample_sharding_and_stats(rtb):
+    nx, ny, ns = 64, 48, 20
+    s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
+    parts = []
+    for r in range(3):
+        o = rtb.default_opts(seed=9, pipeline=rtb.PIPE_POOL, sample_begin=r, sample_stride=3)
+        parts.append(s.render(w, cam, nx, ny, ns, o, want_rgb8=False)[0])
+    whole, _, st = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=9, pipeline=rtb.PIPE_POOL, collect_stats=1), want_rgb8=False,
+                            want_stats=True)
+    np.testing.assert_allclose(parts[0] + parts[1] + parts[2], whole, rtol=1e-4, atol=1e-4)
+    ref, _, sr = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=9, pipeline=rtb.PIPE_MEGAKERNEL, collect_stats=1), want_rgb8=False,
+                          want_stats=True)
+    assert st["node_tests"] == sr["node_tests"] and st["prim_tests"] == sr["prim_tests"] and st["shade"] == sr["shade"]
+
+
 def test_progressive_render_equals_one_shot_and_reports_progress(rtb):
     # chunks of the sample loop add up to the one-shot image (counter-based RNG: same samples), the callback
     # sees monotone progress, previews when asked, and a truthy return stops the render early
