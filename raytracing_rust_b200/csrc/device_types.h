@@ -47,8 +47,10 @@ struct alignas(16) DPrim {
   i4 c;  // (flags, material, first primitive ID, aux)
 };
 
-// 64-byte BVH node holding the boxes of both children (one 4 x LDG.128 burst per visit).
-struct alignas(16) DNode {
+// 64-byte BVH node holding the boxes of both children, fetched as two 256-bit loads per visit
+// (LDG.E.256 on sm_100a: half the L1 wavefronts of four 128-bit loads, and the L1 data pipe is the
+// busiest unit of the traversal, profiles/).
+struct alignas(32) DNode {
   f4 n0;  // child0: lo.x hi.x lo.y hi.y
   f4 n1;  // child1: lo.x hi.x lo.y hi.y
   f4 n2;  // child0 lo.z hi.z, child1 lo.z hi.z

@@ -37,6 +37,7 @@ struct PoolParams {
   int max_depth;
   float t_min;
   int background;
+  int k_leaf;  // hybrid worker: a leaf test runs when at least this many lanes hold a leaf
   int k_node;  // a NODE run goes on while at least this many of the warp's lanes are still at inner nodes
   uint64_t seed;
 };
@@ -45,6 +46,9 @@ struct PoolParams {
 enum { PF_OX = 0, PF_OY, PF_OZ, PF_DX, PF_DY, PF_DZ, PF_TIME, PF_IDX, PF_IDY, PF_IDZ, PF_BEST_T, PF_THR_R, PF_THR_G, PF_THR_B, PF_COUNT };
 enum { PI_BEST_PF = 0, PI_BEST_ID, PI_SELF, PI_PIXEL, PI_SAMPLE, PI_DEPTH, PI_CUR, PI_SP, PI_COUNT };
 
+#ifndef RTB_POOL_HYBRID
+#define RTB_POOL_HYBRID 1
+#endif
 #define POOL_COMPILER_FENCE() asm volatile("" ::: "memory")
 #define PCUR_SHADE (-2147483647 - 1)
 #define PCUR_NEW (-2147483647)
@@ -121,6 +125,78 @@ __global__ void __launch_bounds__(RTB_POOL_THREADS, 1) k_render_pool(SceneView s
     // publisher's state stores land before the atomicOr that sets the slot's bit; only the compiler
     // has to be kept from reordering them.
     POOL_COMPILER_FENCE();
+#if RTB_POOL_HYBRID
+    if (ph <= 1) {
+      // ------------------------------------------------------------------ TRAVERSE worker
+      // Claimed from the NODE or the LEAF queue, so it starts with all its lanes in one phase; it
+      // then keeps alternating node steps and leaf tests for as long as at least k_node / k_leaf of
+      // its lanes want one — a slot only goes back through a queue when the warp's lanes have
+      // drifted apart (or its traversal is done).
+      RayF ray;
+      ray.o = mk(0.f, 0.f, 0.f), ray.d = mk(0.f, 0.f, 1.f), ray.time = 0.f;
+      RayInv ri;
+      ri.idx = ri.idy = ri.idz = 1.f, ri.oodx = ri.oody = ri.oodz = 0.f;
+      float best_t = 0.f;
+      int best_pf = -1, best_id = -1, self = -1, cur = PCUR_SHADE, sp = 0;
+      if (cand) {
+        ray.o = mk(F[PF_OX][rr][lane], F[PF_OY][rr][lane], F[PF_OZ][rr][lane]);
+        ray.d = mk(F[PF_DX][rr][lane], F[PF_DY][rr][lane], F[PF_DZ][rr][lane]);
+        ray.time = F[PF_TIME][rr][lane];
+        ri.idx = F[PF_IDX][rr][lane], ri.idy = F[PF_IDY][rr][lane], ri.idz = F[PF_IDZ][rr][lane];
+        ri.oodx = ray.o.x * ri.idx, ri.oody = ray.o.y * ri.idy, ri.oodz = ray.o.z * ri.idz;
+        best_t = F[PF_BEST_T][rr][lane];
+        best_pf = I[PI_BEST_PF][rr][lane], best_id = I[PI_BEST_ID][rr][lane], self = I[PI_SELF][rr][lane];
+        cur = I[PI_CUR][rr][lane], sp = I[PI_SP][rr][lane];
+      }
+      const bool act = cand && ((claimed >> rr) & 1u);
+      if (!act) cur = PCUR_SHADE;
+      bool first = true;
+      for (;;) {
+        const int n_node = __popc(__ballot_sync(0xffffffffu, cur >= 0));
+        if (n_node >= P.k_node || (first && ph == 0 && n_node > 0)) {
+          first = false;
+          if (cur >= 0) {
+            if (kStats) cnt.node_tests++;
+            int next, push;
+            const int nh = node_step(sv.nodes, cur, ri, P.t_min, best_t, &next, &push);
+            if (nh == 2) STK[sp++][rr][lane] = push;
+            if (nh == 0) next = sp > 0 ? STK[--sp][rr][lane] : PCUR_SHADE;
+            cur = next;
+          }
+          continue;
+        }
+        const bool at_leaf = cur < 0 && cur != PCUR_SHADE;
+        const int n_leaf = __popc(__ballot_sync(0xffffffffu, at_leaf));
+        if (n_leaf >= P.k_leaf || (first && n_leaf > 0)) {
+          first = false;
+          if (at_leaf) {
+            const float inv_a = rcp_fast(dot(ray.d, ray.d));
+            const unsigned code = ~(unsigned)cur;
+            const int lfirst = (int)(code >> 3), count = (int)(code & 7u);
+            for (int q = 0; q < count; ++q) {
+              const int pi = lfirst + q;
+              float t;
+              int face, id;
+              if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, P.t_min, best_t, pi == (self >> 3), self & 7, &t,
+                                         &face, &id, &cnt) &&
+                  (t < best_t || id > best_id)) {
+                best_t = t, best_pf = (pi << 3) | face, best_id = id;
+              }
+            }
+            cur = sp > 0 ? STK[--sp][rr][lane] : PCUR_SHADE;
+          }
+          continue;
+        }
+        break;
+      }
+      if (act) {
+        F[PF_BEST_T][rr][lane] = best_t;
+        I[PI_BEST_PF][rr][lane] = best_pf, I[PI_BEST_ID][rr][lane] = best_id;
+        I[PI_CUR][rr][lane] = cur, I[PI_SP][rr][lane] = sp;
+        POOL_COMPILER_FENCE();
+        atomicOr(&Q[cur >= 0 ? 0 : (cur == PCUR_SHADE ? 2 : 1)][lane], 1u << rr);
+      }
+#else
     if (ph == 0) {
       // ------------------------------------------------------------------ NODE worker
       RayInv ri;
@@ -183,6 +259,7 @@ __global__ void __launch_bounds__(RTB_POOL_THREADS, 1) k_render_pool(SceneView s
         POOL_COMPILER_FENCE();
         atomicOr(&Q[cur >= 0 ? 0 : (cur == PCUR_SHADE ? 2 : 1)][lane], 1u << rr);
       }
+#endif
     } else {
       // ------------------------------------------------------------------ SHADE worker
       const bool act = cand && ((claimed >> rr) & 1u);
@@ -355,7 +432,8 @@ int launch_pool(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, cons
     P.tiles_x = (int)tiles_x;
     P.total_ids = (unsigned)(tiles * 32 * P.sample_count);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
-    P.k_node = std::max(1, o.reserved[0] > 0 ? o.reserved[0] : 16);
+    P.k_node = std::max(1, o.reserved[0] > 0 ? o.reserved[0] : 8);
+    P.k_leaf = std::max(1, o.reserved[1] > 0 ? o.reserved[1] : 8);
     int rc;
     if (o.collect_stats)
       rc = launch_pool_variant<true, RTB_POOL_ROWS, RTB_POOL_STACK>(d, cam, P, d_sum, stream);

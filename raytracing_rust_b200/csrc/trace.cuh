@@ -35,6 +35,17 @@ __device__ __forceinline__ void set_comp(V3f& v, int axis, float s) {
 
 __device__ __forceinline__ float4 ldg4(const f4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
 __device__ __forceinline__ int4 ldg4i(const i4* p) { return __ldg(reinterpret_cast<const int4*>(p)); }
+// one 256-bit read-only load (sm_100a: ld.global.nc.v8.f32 -> LDG.E.256.CONSTANT); p is 32-byte aligned
+struct alignas(32) Ld256 {
+  float v[8];
+};
+__device__ __forceinline__ Ld256 ld256(const Ld256* p) {
+  Ld256 r;
+  asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
+      : "l"(p));
+  return r;
+}
 
 // Single-instruction SFU forms (MUFU.RCP / RSQ / SQRT / EX2 / LG2, <= 2 ulp).  The f64 reference
 // is matched statistically and through closest-hit IDs, not bit-wise, so the IEEE-rounded
@@ -265,9 +276,12 @@ __device__ __forceinline__ RayInv make_ray_inv(const RayF& ray) {
 // (valid when 2 is returned).
 __device__ __forceinline__ int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
                                          int* next, int* push) {
-  const DNode* nd = nodes + cur;
-  const float4 n0 = ldg4(&nd->n0), n1 = ldg4(&nd->n1), n2 = ldg4(&nd->n2);
-  const int4 n3 = ldg4i(&nd->n3);
+  // two 256-bit loads (LDG.E.256.CONSTANT): (n0, n1) and (n2, n3)
+  const Ld256 h0v = ld256(reinterpret_cast<const Ld256*>(nodes + cur));
+  const Ld256 h1v = ld256(reinterpret_cast<const Ld256*>(nodes + cur) + 1);
+  const float4 n0 = make_float4(h0v.v[0], h0v.v[1], h0v.v[2], h0v.v[3]), n1 = make_float4(h0v.v[4], h0v.v[5], h0v.v[6], h0v.v[7]);
+  const float4 n2 = make_float4(h1v.v[0], h1v.v[1], h1v.v[2], h1v.v[3]);
+  const int4 n3 = make_int4(__float_as_int(h1v.v[4]), __float_as_int(h1v.v[5]), __float_as_int(h1v.v[6]), __float_as_int(h1v.v[7]));
   float c0lox = fmaf(n0.x, ri.idx, -ri.oodx), c0hix = fmaf(n0.y, ri.idx, -ri.oodx);
   float c0loy = fmaf(n0.z, ri.idy, -ri.oody), c0hiy = fmaf(n0.w, ri.idy, -ri.oody);
   float c0loz = fmaf(n2.x, ri.idz, -ri.oodz), c0hiz = fmaf(n2.y, ri.idz, -ri.oodz);
