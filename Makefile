@@ -6,9 +6,10 @@ LIB ?= raytracing_rust_b200/librtb200.so
 # experiment builds: make B=build/x LIB=build/x/librtb200.so EXTRA=-DRTB_FOO=1 lib
 B ?= build
 EXTRA ?=
+NVEXTRA ?=
 GENCODE := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := -O3 -std=c++17 $(GENCODE) -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unknown-pragmas -Iinclude -I$(CSRC) \
-             -Xptxas -v --expt-relaxed-constexpr $(EXTRA)
+             -Xptxas -v --expt-relaxed-constexpr $(EXTRA) $(NVEXTRA)
 HOST_SRCS := $(CSRC)/scene.cpp $(CSRC)/scenes_named.cpp $(CSRC)/flatten.cpp
 CU_SRCS := $(CSRC)/render.cu $(CSRC)/wavefront.cu $(CSRC)/peer.cu $(CSRC)/pool.cu
 HDRS := $(wildcard include/*.h include/*.hpp $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh)

@@ -536,8 +536,15 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     const long long blocks = std::min<long long>((items + wpb - 1) / wpb, (long long)d->prop.multiProcessorCount * min_blocks);
     unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
     CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
-#define RTB_LAUNCH_MEGA(ST, TH, MB) \
-  k_render_mega<ST, TH, MB><<<(unsigned)blocks, TH, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc)
+    // Shared-memory carveout: just what the resident blocks need (13.3 KB static + 1 KB reserved each), the rest of the
+    // 228 KB array stays L1 — the BVH (90 KB) and primitives (68 KB) live there and throughput follows the L1 size
+    // (carveout 100 %: -21 %, profiles/r1_experiments.txt).  o.reserved[5] overrides for experiments.
+    const int carveout = o.reserved[5] > 0 ? o.reserved[5] : std::min(100, (min_blocks * (14 * 1024 + 1024) * 100) / (228 * 1024) + 5);
+#define RTB_LAUNCH_MEGA(ST, TH, MB)                                                                                   \
+  do {                                                                                                                \
+    cudaFuncSetAttribute(k_render_mega<ST, TH, MB>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);        \
+    k_render_mega<ST, TH, MB><<<(unsigned)blocks, TH, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);           \
+  } while (0)
     if (o.collect_stats) {
       if (block == 256) RTB_LAUNCH_MEGA(true, 256, 2); else RTB_LAUNCH_MEGA(true, 128, 4);
     } else {

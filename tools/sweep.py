@@ -10,12 +10,14 @@ o = rtb.default_opts(collect_stats=1)
 _, _, st = s.render(w, cam, nx, ny, 4, o, want_sum=False, want_rgb8=False, want_stats=True)
 print(name, {k: (round(v / st["segments"], 2) if k.endswith("tests") else v) for k, v in st.items() if k in ("node_tests", "prim_tests", "medium_tests", "segments", "paths")})
 grid = [tuple(int(x) for x in a.split(",")) for a in sys.argv[5:]] or [(16, 8, 8, 3)]
-for kn, kl, ks, mb in grid:
+for knobs in grid:  # k_node, k_leaf, k_shade, occupancy point[, -, smem carveout %]
+    kn, kl, ks, mb = knobs[:4]
     o = rtb.default_opts()
-    o.reserved[0], o.reserved[1], o.reserved[2], o.reserved[3] = kn, kl, ks, mb
+    for i, k in enumerate(knobs):
+        o.reserved[i] = k
     s.render(w, cam, nx, ny, 2, o, want_sum=False, want_rgb8=False)
     best = 1e9
     for _ in range(2):
         _, _, st = s.render(w, cam, nx, ny, ns, o, want_sum=False, want_rgb8=False, want_stats=True)
         best = min(best, st["device_ms"])
-    print(f"k_node {kn:2d} k_leaf {kl:2d} k_shade {ks:2d} minblocks {mb}: {best:8.2f} ms {st['paths']/best/1e3:8.1f} Mpaths/s", flush=True)
+    print(f"k_node {kn:2d} k_leaf {kl:2d} k_shade {ks:2d} minblocks {mb} extra {knobs[4:]}: {best:8.2f} ms {st['paths']/best/1e3:8.1f} Mpaths/s", flush=True)
