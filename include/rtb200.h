@@ -113,6 +113,15 @@ rtb_scene* rtb_scene_load(const char* path);
  * in the order of src/cube.rs:21-74) */
 int rtb_scene_prim_count(rtb_scene*, int world);
 
+/* Who builds the BVH the kernels traverse (BVHNode::new, src/bvh.rs:17-66, is a host recursion
+ * upstream; closest-hit answers do not depend on the tree).  HOST_SAH: full-sweep SAH on the host
+ * (best trees).  DEVICE_LBVH: Morton-sorted linear BVH built by CUDA kernels (csrc/bvh_build.cu),
+ * for large scenes.  AUTO: the device builder from RTB_BVH_AUTO_DEVICE_MIN primitive IDs on.
+ * Takes effect at the next upload. */
+typedef enum RtbBvhBuilder { RTB_BVH_AUTO = 0, RTB_BVH_HOST_SAH = 1, RTB_BVH_DEVICE_LBVH = 2 } RtbBvhBuilder;
+#define RTB_BVH_AUTO_DEVICE_MIN 100000
+int rtb_scene_set_bvh_builder(rtb_scene*, int builder);
+
 /* ---- rendering ---------------------------------------------------------------------------- */
 typedef struct rtb_render_opts {
   int max_depth;       /* 50  (src/color.rs:9) */

@@ -31,6 +31,7 @@ lib = C.CDLL(str(_LIB_PATH))
 PLANE_YZ, PLANE_ZX, PLANE_XY = 0, 1, 2
 AXIS_X, AXIS_Y, AXIS_Z = 0, 1, 2
 BG_BLACK, BG_SKY = 0, 1
+BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
 PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_POOL = 0, 1, 2, 3
 
 NAMED_SCENES = (
@@ -113,6 +114,7 @@ _sig("rtb_scene_serialized_size", _sz, _vp)
 _sig("rtb_scene_serialize", _i, _vp, _vp, _sz)
 _sig("rtb_scene_deserialize", _vp, _vp, _sz)
 _sig("rtb_scene_prim_count", _i, _vp, _i)
+_sig("rtb_scene_set_bvh_builder", _i, _vp, _i)
 _sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
 _sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
 PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_double, C.c_double)
@@ -297,6 +299,10 @@ class Scene:
         if not p:
             raise RtbError(-1, "scene_load")
         return cls(_ptr=p)
+
+    def set_bvh_builder(self, builder: int):
+        """BVH_AUTO / BVH_HOST_SAH / BVH_DEVICE_LBVH; takes effect at the next upload."""
+        _h(lib.rtb_scene_set_bvh_builder(self._p, builder), "scene_set_bvh_builder")
 
     def prim_count(self, world):
         return _h(lib.rtb_scene_prim_count(self._p, world), "scene_prim_count")

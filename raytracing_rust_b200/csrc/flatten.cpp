@@ -305,7 +305,7 @@ void pad_box(const Box3& b, float lo[3], float hi[3]) {
 
 }  // namespace
 
-int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi, FlatScene* out) {
+int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi, FlatScene* out, bool host_bvh) {
   if (world < 0 || (size_t)world >= s.obj.size()) return fail(RTB_ERR_INVALID, "flatten: bad world handle");
   *out = FlatScene();
   out->time_lo = time_lo, out->time_hi = time_hi;
@@ -354,6 +354,14 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
     dn.n3 = {~0, ~0, 0, 0};
     out->nodes.push_back(dn);
     out->root = 0;
+    return RTB_OK;
+  }
+  if (!host_bvh && n >= 2) {
+    // the BVH is built on the device (bvh_build.cu): hand over the primitives in insertion order and
+    // their conservatively padded f32 boxes (lo.xyz, hi.xyz)
+    out->prim_boxes.resize((size_t)n * 6);
+    for (int i = 0; i < n; ++i) pad_box(w.prim_boxes[i], &out->prim_boxes[(size_t)i * 6], &out->prim_boxes[(size_t)i * 6 + 3]);
+    out->root = -1;
     return RTB_OK;
   }
   Builder b{w.prim_boxes, {}, {}};

@@ -18,6 +18,7 @@ struct FlatScene {
   std::vector<DTexture> texs;
   std::vector<DPerlin> perlin;
   std::vector<uint32_t> texels;
+  std::vector<float> prim_boxes;  // n x (lo.xyz, hi.xyz), only when the BVH is left to the device builder
   int root = -1;
   int n_prim_ids = 0;
   int bvh_depth = 0;
@@ -26,6 +27,7 @@ struct FlatScene {
 };
 
 // Returns 0 or an RtbStatus error (message via set_error).
-int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi, FlatScene* out);
+// host_bvh = false leaves `nodes` empty (root = -1) and fills `prim_boxes` for the device builder.
+int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi, FlatScene* out, bool host_bvh = true);
 
 }  // namespace rtb

@@ -435,7 +435,10 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   }
   DeviceScene* d = new DeviceScene();
   d->device = device;
-  int rc = flatten_scene(*s, world, tlo, thi, &d->flat);
+  // who builds the BVH: the host's full-sweep SAH (best trees; O(n log^2 n)) or the device LBVH (bvh_build.cu)
+  int builder = s->bvh_builder;
+  if (builder == RTB_BVH_AUTO) builder = rtb_scene_prim_count(s, world) >= RTB_BVH_AUTO_DEVICE_MIN ? RTB_BVH_DEVICE_LBVH : RTB_BVH_HOST_SAH;
+  int rc = flatten_scene(*s, world, tlo, thi, &d->flat, builder != RTB_BVH_DEVICE_LBVH);
   if (rc != RTB_OK) {
     delete d;
     return rc;
@@ -443,15 +446,25 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   CUDA_TRY(cudaSetDevice(device));
   SceneView& v = d->view;
   const FlatScene& f = d->flat;
-  if ((rc = upload_vec(d, f.nodes, &v.nodes)) || (rc = upload_vec(d, f.prims, &v.prims)) ||
-      (rc = upload_vec(d, f.bprims, &v.bprims)) || (rc = upload_vec(d, f.media, &v.media)) ||
+  const bool device_bvh = f.root < 0;  // flatten left the tree to the device builder
+  if (device_bvh) {
+    if ((rc = build_bvh_device(d)) != RTB_OK) {
+      destroy_device_scene(d);
+      return rc;
+    }
+  } else if ((rc = upload_vec(d, f.nodes, &v.nodes)) || (rc = upload_vec(d, f.prims, &v.prims))) {
+    destroy_device_scene(d);
+    return rc;
+  }
+  if ((rc = upload_vec(d, f.bprims, &v.bprims)) || (rc = upload_vec(d, f.media, &v.media)) ||
       (rc = upload_vec(d, f.xforms, &v.xforms)) || (rc = upload_vec(d, f.mats, &v.mats)) ||
       (rc = upload_vec(d, f.texs, &v.texs)) || (rc = upload_vec(d, f.perlin, &v.perlin)) ||
       (rc = upload_vec(d, f.texels, &v.texels))) {
     destroy_device_scene(d);
     return rc;
   }
-  v.n_nodes = (int)f.nodes.size(), v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
+  if (!device_bvh) v.n_nodes = (int)f.nodes.size(), d->n_nodes_device = v.n_nodes;
+  v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
   v.root = f.root;
   void* st = nullptr;
   CUDA_TRY(cudaMalloc(&st, 32 * sizeof(unsigned long long)));
@@ -465,8 +478,8 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   s->dev = d;
   s->dev_world = world;
   if (std::getenv("RTB200_DEBUG"))
-    std::fprintf(stderr, "[rtb200] uploaded: %zu nodes, %zu prims, %zu boundary prims, %zu media, %zu xforms, bvh depth %d\n",
-                 f.nodes.size(), f.prims.size(), f.bprims.size(), f.media.size(), f.xforms.size(), f.bvh_depth);
+    std::fprintf(stderr, "[rtb200] uploaded: %d nodes (%s), %zu prims, %zu boundary prims, %zu media, %zu xforms, bvh depth %d\n",
+                 d->n_nodes_device, device_bvh ? "device LBVH" : "host SAH", f.prims.size(), f.bprims.size(), f.media.size(), f.xforms.size(), f.bvh_depth);
   return RTB_OK;
 }
 
@@ -594,7 +607,7 @@ int rtb_scene_upload(rtb_scene* s, int world, int device) { return ensure_upload
 size_t rtb_scene_device_bytes(const rtb_scene* s) {
   if (!s || !s->dev) return 0;
   const FlatScene& f = s->dev->flat;
-  return f.nodes.size() * sizeof(DNode) + (f.prims.size() + f.bprims.size()) * sizeof(DPrim) +
+  return (size_t)s->dev->n_nodes_device * sizeof(DNode) + (f.prims.size() + f.bprims.size()) * sizeof(DPrim) +
          f.media.size() * sizeof(DMedium) + f.xforms.size() * sizeof(DXform) + f.mats.size() * sizeof(DMaterial) +
          f.texs.size() * sizeof(DTexture) + f.perlin.size() * sizeof(DPerlin) + f.texels.size() * sizeof(uint32_t);
 }

@@ -22,7 +22,11 @@ struct DeviceScene {
   unsigned int* d_work = nullptr;         // work-item counter of the running megakernel launch
   cudaDeviceProp prop{};
   WavefrontState* wf = nullptr;
+  int n_nodes_device = 0;  // BVH nodes resident on the device (host- or device-built)
 };
+
+// bvh_build.cu: LBVH over d->flat.prims on the device; sets view.nodes / view.prims / flat.root / flat.bvh_depth
+int build_bvh_device(DeviceScene* d);
 
 int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi);
 void make_device_camera(const RtbCamera& c, DCamera* out);

@@ -425,6 +425,17 @@ size_t rtb_ppm_p3(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap) {
   return s.size();
 }
 
+int rtb_scene_set_bvh_builder(rtb_scene* s, int builder) {
+  CHECK_SCENE(s);
+  if (builder < RTB_BVH_AUTO || builder > RTB_BVH_DEVICE_LBVH) return fail(RTB_ERR_INVALID, "set_bvh_builder: bad builder");
+  if (s->bvh_builder != builder && s->dev) {  // rebuild at the next upload
+    rtb::destroy_device_scene(s->dev);
+    s->dev = nullptr;
+  }
+  s->bvh_builder = builder;
+  return RTB_OK;
+}
+
 size_t rtb_ppm_p6(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap) {
   // binary sibling of the P3 text above: same header fields, raw bytes, rows top to bottom
   std::string hdr = "P6\n" + std::to_string(nx) + " " + std::to_string(ny) + "\n255\n";

@@ -41,6 +41,7 @@ struct rtb_scene {
   std::vector<uint8_t> image_pool;
   rtb::DeviceScene* dev = nullptr;  // uploaded flattened scene (rtb_scene_upload)
   int dev_world = -1;
+  int bvh_builder = 0;  // RtbBvhBuilder
   ~rtb_scene() {
     if (dev) rtb::destroy_device_scene(dev);
   }
