@@ -44,7 +44,8 @@ enum RtbPipeline {
   RTB_PIPE_AUTO = 0,
   RTB_PIPE_MEGAKERNEL = 1, /* one persistent kernel, path regeneration */
   RTB_PIPE_WAVEFRONT = 2,  /* raygen / extend / per-material shade queues, path state in HBM */
-  RTB_PIPE_POOL = 3        /* per-SM path pool in shared memory, warps regroup paths by phase */
+  RTB_PIPE_POOL = 3,       /* per-SM path pool in shared memory, warps regroup paths by phase */
+  RTB_PIPE_DUAL = 4        /* the megakernel's scheduler with two paths per lane (state in shared memory) */
 };
 
 const char* rtb_last_error(void);

@@ -32,7 +32,7 @@ PLANE_YZ, PLANE_ZX, PLANE_XY = 0, 1, 2
 AXIS_X, AXIS_Y, AXIS_Z = 0, 1, 2
 BG_BLACK, BG_SKY = 0, 1
 BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
-PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_POOL = 0, 1, 2, 3
+PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_POOL, PIPE_DUAL = 0, 1, 2, 3, 4
 
 NAMED_SCENES = (
     "random_scene", "two_spheres", "two_perlin_sphere", "earth", "simple_light",

@@ -43,6 +43,9 @@ void make_device_camera(const RtbCamera& c, DCamera* out);
 bool pool_supports(const DeviceScene* d);
 int launch_pool(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
                 cudaStream_t stream, uint64_t* launches);
+// dual.cu: the megakernel's scheduler with two paths per lane (RTB_PIPE_DUAL)
+int launch_dual(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
+                cudaStream_t stream, uint64_t* launches);
 int launch_wavefront(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
                      cudaStream_t stream, uint64_t* launches);
 

@@ -276,6 +276,21 @@ def test_pool_sample_sharding_and_stats(rtb):
     assert st["node_tests"] == sr["node_tests"] and st["prim_tests"] == sr["prim_tests"] and st["shade"] == sr["shade"]
 
 
+# ---- 8b. two paths per lane (RTB_PIPE_DUAL): same draws, same device functions, same counters -------------------
+@pytest.mark.parametrize("name,bg,nx,ny", [("cornell_box", 0, 96, 64), ("final_scene_lit", 0, 96, 64), ("random_scene", 1, 93, 61),
+                                           ("cornell_smoke_book", 0, 96, 64), ("earth", 1, 37, 19)])
+def test_dual_equals_megakernel(rtb, name, bg, nx, ny):
+    ns = 24
+    s, w, cam = rtb.Scene.named(name, nx, ny)
+    kw = dict(background=bg, seed=4, collect_stats=1, sample_begin=1, sample_stride=2)
+    a, _, sa = s.render(w, cam, nx, ny, ns, rtb.default_opts(pipeline=rtb.PIPE_MEGAKERNEL, **kw), want_rgb8=False, want_stats=True)
+    b, _, sb = s.render(w, cam, nx, ny, ns, rtb.default_opts(pipeline=rtb.PIPE_DUAL, **kw), want_rgb8=False, want_stats=True)
+    assert sb["paths"] == nx * ny * (ns // 2)
+    for k in ("segments", "node_tests", "prim_tests", "shade"):
+        assert sa[k] == sb[k], k
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)  # identical paths; only the order of the float adds differs
+
+
 def test_progressive_render_equals_one_shot_and_reports_progress(rtb):
     # chunks of the sample loop add up to the one-shot image (counter-based RNG: same samples), the callback
     # sees monotone progress, previews when asked, and a truthy return stops the render early
