@@ -270,11 +270,13 @@ def run_gpu(args):
     achieved = work_per_step / (kern_ms / args.steps * 1e-3) / 1e12
     roofline = {
         "bound": "fp32_issue", "achieved": achieved, "peak": issue_peak, "unit": "Tlane-instr/s",
-        "frac": achieved / issue_peak, "traffic": None,
+        "frac": achieved / issue_peak, "traffic": ncu_traffic_bytes(NX, NY, spp),
         "note": ("SURVEY.md §8(d): scene tables (<1 MB + 1.5 MB texture) stay in L1/L2, no dense contraction, so the bound is "
                  "SM instruction issue: peak = SMs x 128 lanes x SM clock sampled during the run; achieved = algorithmic "
                  "lane-instructions (fixed cost table x device op counters of one step) / kernel time. "
-                 "MEASURED_PEAKS.json has no FP32 entry; HBM traffic per launch is ~2 MB (ncu, profiles/)."),
+                 "MEASURED_PEAKS.json has no FP32 entry. traffic = dram bytes read + written by one launch of this "
+                 "workload (ncu, profiles/r1_mega_traffic_4k64.csv): megabytes against the algorithmic image + scene "
+                 "tables, i.e. HBM is idle; L2 sees 348 GB per launch (traversal-stack write-through)."),
         "segments_per_path": st["segments"] / st["paths"], "node_tests_per_segment": st["node_tests"] / st["segments"],
         "prim_tests_per_segment": st["prim_tests"] / st["segments"],
         "lane_instr_per_segment_model": work_per_step / st["segments"],
@@ -299,6 +301,21 @@ def run_gpu(args):
     os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic_bytes(nx, ny, spp):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_render_mega launch, from the committed ncu capture of
+    exactly this launch shape (profiles/r1_mega_traffic_4k64.csv: 3840x2160, 64 spp); None for any other shape."""
+    import csv
+    f = ROOT / "profiles" / "r1_mega_traffic_4k64.csv"
+    if (nx, ny, spp) != (3840, 2160, 64) or not f.exists():
+        return None
+    per_launch = {}
+    for r in csv.DictReader(l for l in open(f) if l.startswith('"')):
+        if r["Metric Name"].startswith("dram__bytes"):
+            per_launch.setdefault(r["ID"], 0.0)
+            per_launch[r["ID"]] += float(r["Metric Value"])
+    return sum(per_launch.values()) / len(per_launch) if per_launch else None
 
 
 def main():
