@@ -203,6 +203,17 @@ int rtb_peer_close(void* d_ptr);
 int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, int ny, int ns,
                               float* d_total, uint8_t* d_rgb8, void* cuda_stream);
 
+/* create_image on several GPUs of this node from one call (csrc/multi.cu): one host thread per
+ * device renders the sample slice s = i, i+G, ... of every pixel, then devices[0] sums the G
+ * partial images over peer access and quantises them in one kernel (rtb_reduce_resolve_device).
+ * devices == NULL: ordinals 0 .. n_devices-1 (n_devices <= 0: every visible device).  The image is
+ * the one rtb_render produces for the same seed, whatever G is (the draws are counter-based), up
+ * to the order of the float adds.  opts->device and the sample_begin/stride fields are ignored /
+ * must be 0,1.  stats (optional): sums over the devices, device_ms = the slowest shard,
+ * reserved[0] = G. */
+int rtb_render_multi(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns, const rtb_render_opts*,
+                     const int* devices, int n_devices, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
+
 /* Closest-hit query for the primitive-ID parity test: Hittable::hit(ray, t_min, f64::MAX)
  * (src/color.rs:7) with ConstantMedium objects skipped.  rays = n x {ox,oy,oz,dx,dy,dz,time}
  * (host, double); out_prim[i] = primitive ID or -1; out_t[i] = t (undefined on a miss). */

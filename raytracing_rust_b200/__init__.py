@@ -117,6 +117,8 @@ _sig("rtb_scene_prim_count", _i, _vp, _i)
 _sig("rtb_scene_set_bvh_builder", _i, _vp, _i)
 _sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
 _sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
+_sig("rtb_render_multi", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), C.POINTER(C.c_int), _i, _vp, _vp,
+     C.POINTER(Stats))
 PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_double, C.c_double)
 _sig("rtb_render_progressive", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _i, _i, PROGRESS_FN, _vp,
      _vp, _vp, C.POINTER(C.c_int))
@@ -319,6 +321,25 @@ class Scene:
                           out_sum.ctypes.data if want_sum else None, out_rgb8.ctypes.data if want_rgb8 else None,
                           C.byref(st) if want_stats else None), "render")
         return out_sum, out_rgb8, (st.as_dict() if want_stats else None)
+
+    def render_multi(self, world, cam, nx, ny, ns, devices=None, opts=None, want_sum=True, want_rgb8=True, want_stats=False):
+        """create_image on several GPUs of this node from one call (rtb_render_multi): samples sharded over
+        `devices` (list of ordinals, an int = the first n, None = all), partial sums combined on devices[0]."""
+        o = opts if opts is not None else default_opts()
+        out_sum = np.empty((ny, nx, 3), np.float32) if want_sum else None
+        out_rgb8 = np.empty((ny, nx, 3), np.uint8) if want_rgb8 else None
+        st = Stats() if want_stats else None
+        if devices is None or isinstance(devices, int):
+            arr, n = None, (devices or 0)
+        else:
+            arr, n = (C.c_int * len(devices))(*devices), len(devices)
+        _h(lib.rtb_render_multi(self._p, world, C.byref(cam), nx, ny, ns, C.byref(o), arr, n,
+                                out_sum.ctypes.data if want_sum else None, out_rgb8.ctypes.data if want_rgb8 else None,
+                                C.byref(st) if want_stats else None), "render_multi")
+        d = st.as_dict() if want_stats else None
+        if d is not None:
+            d["devices"] = int(st.reserved[0])
+        return out_sum, out_rgb8, d
 
     def render_progressive(self, world, cam, nx, ny, ns, chunk_spp, on_progress=None, preview_every=0, opts=None, want_sum=False):
         """create_image in chunks with real progress (rtb_render_progressive).  on_progress(done, total,

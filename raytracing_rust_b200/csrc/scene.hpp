@@ -42,7 +42,12 @@ struct rtb_scene {
   rtb::DeviceScene* dev = nullptr;  // uploaded flattened scene (rtb_scene_upload)
   int dev_world = -1;
   int bvh_builder = 0;  // RtbBvhBuilder
+  // rtb_render_multi: copies of this scene for the other devices (one device copy per handle) and the
+  // serialised bytes they were made from
+  std::vector<rtb_scene*> replicas;
+  std::vector<uint8_t> replica_blob;
   ~rtb_scene() {
+    for (rtb_scene* r : replicas) delete r;
     if (dev) rtb::destroy_device_scene(dev);
   }
   bool tex_ok(int h) const { return h >= 0 && (size_t)h < tex.size(); }

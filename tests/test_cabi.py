@@ -141,6 +141,9 @@ def test_no_device_is_a_loud_error(rtb):
     with pytest.raises(rtb.RtbError) as e:
         s.render(w, cam, 8, 8, 1)
     assert e.value.code == -2  # RTB_ERR_NO_DEVICE: no CPU fallback
+    with pytest.raises(rtb.RtbError) as e:
+        s.render_multi(w, cam, 8, 8, 1)
+    assert e.value.code == -2
 
 
 def test_primary_rays_are_deterministic_and_in_frustum(rtb):

@@ -71,3 +71,45 @@ def test_two_gpu_peer_reduce_equals_single_gpu_image():
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "peer reduce ok" in r.stdout
+
+
+# ---- rtb_render_multi: create_image on several GPUs from one host call (csrc/multi.cu) --------------------------
+def test_render_multi_on_one_device_is_render():
+    nx, ny, ns = 96, 64, 12
+    s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
+    a_sum, a8, sa = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=5), want_stats=True)
+    b_sum, b8, sb = s.render_multi(w, cam, nx, ny, ns, devices=[0], opts=rtb.default_opts(seed=5), want_stats=True)
+    np.testing.assert_array_equal(a_sum, b_sum)
+    np.testing.assert_array_equal(a8, b8)
+    assert sb["devices"] == 1 and sb["paths"] == sa["paths"] == nx * ny * ns and sb["segments"] == sa["segments"]
+    assert sb["kernel_launches"] == sa["kernel_launches"] + 1
+    with pytest.raises(rtb.RtbError):
+        s.render_multi(w, cam, nx, ny, ns, devices=[0, 0])
+    with pytest.raises(rtb.RtbError):
+        s.render_multi(w, cam, nx, ny, ns, devices=[0, 99])
+    with pytest.raises(rtb.RtbError):
+        s.render_multi(w, cam, nx, ny, ns, devices=[0], opts=rtb.default_opts(sample_begin=1, sample_stride=2))
+
+
+def test_render_multi_all_devices_equals_single_gpu_image():
+    n_dev = rtb.device_count()
+    if n_dev < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nx, ny, ns = 203, 117, 21  # ragged everything: ns not a multiple of the device count
+    for name, bg in (("final_scene_lit", 0), ("random_scene", 1)):
+        s, w, cam = rtb.Scene.named(name, nx, ny)
+        o = rtb.default_opts(seed=11, background=bg)
+        a_sum, a8, sa = s.render(w, cam, nx, ny, ns, o, want_stats=True)
+        for devs in (None, list(range(n_dev))[::-1], 2):
+            b_sum, b8, sb = s.render_multi(w, cam, nx, ny, ns, devices=devs, opts=o, want_stats=True)
+            # same sample set (counter-based draws), different float add order
+            np.testing.assert_allclose(a_sum, b_sum, rtol=1e-4, atol=1e-4)
+            assert np.abs(a8.astype(int) - b8.astype(int)).max() <= 1
+            assert sb["paths"] == sa["paths"] and sb["segments"] == sa["segments"]
+            assert sb["devices"] == (2 if devs == 2 else min(n_dev, ns))
+    # more devices than samples: the surplus devices stay idle
+    s, w, cam = rtb.Scene.named("two_spheres", 64, 36)
+    one_sum, _, _ = s.render(w, cam, 64, 36, 1, rtb.default_opts(background=1))
+    m_sum, _, st = s.render_multi(w, cam, 64, 36, 1, opts=rtb.default_opts(background=1), want_stats=True)
+    np.testing.assert_array_equal(one_sum, m_sum)
+    assert st["devices"] == 1
