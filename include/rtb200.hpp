@@ -332,13 +332,18 @@ struct LoweredScene {
 
 // create_image(ny, nx, ns, cam, world) -> String, tests/test.rs:55-85 — same argument order
 // (ny before nx), same P3 text out; the pixel loop runs on the GPU.
+// n_gpus: 1 = the device in opts (default 0); 0 = every GPU of the node, k > 1 = the first k (rtb_render_multi).
 inline std::string create_image(size_t ny, size_t nx, size_t ns, const Camera& cam, const Hittable& world,
-                                const rtb_render_opts* opts = nullptr) {
+                                const rtb_render_opts* opts = nullptr, int n_gpus = 1) {
   LoweredScene ls(world);
   rtb_render_opts o;
   if (opts) o = *opts; else rtb_render_opts_default(&o);
   std::vector<uint8_t> rgb8(3 * nx * ny);
-  if (rtb_render(ls.scene, ls.world, &cam.c, (int)nx, (int)ny, (int)ns, &o, nullptr, rgb8.data(), nullptr) != 0)
+  const int rc = n_gpus == 1
+                     ? rtb_render(ls.scene, ls.world, &cam.c, (int)nx, (int)ny, (int)ns, &o, nullptr, rgb8.data(), nullptr)
+                     : rtb_render_multi(ls.scene, ls.world, &cam.c, (int)nx, (int)ny, (int)ns, &o, nullptr, n_gpus, nullptr,
+                                        rgb8.data(), nullptr);
+  if (rc != 0)
     throw std::runtime_error(std::string("create_image: ") + rtb_last_error());
   size_t n = rtb_ppm_p3(rgb8.data(), (int)nx, (int)ny, nullptr, 0);
   std::string out(n, '\0');

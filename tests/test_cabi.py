@@ -32,6 +32,26 @@ def test_header_compiles_as_c(tmp_path):
                     str(tmp_path / "t.o")], check=True)
 
 
+def build_cpp_scene_test(tmp_path):
+    """tests/cpp/test_scenes.cpp: the reference's #[test] bodies against include/rtb200.hpp, linked to librtb200.so"""
+    import subprocess
+    exe = tmp_path / "test_scenes"
+    libdir = ROOT / "raytracing_rust_b200"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I", str(ROOT / "include"),
+                    str(ROOT / "tests" / "cpp" / "test_scenes.cpp"), "-o", str(exe), "-L", str(libdir), "-lrtb200",
+                    f"-Wl,-rpath,{libdir}"], check=True)
+    return exe
+
+
+def test_cpp_host_api_builds_and_fails_loudly_without_a_gpu(rtb, tmp_path):
+    import subprocess
+    exe = build_cpp_scene_test(tmp_path)
+    if rtb.device_count() > 0:
+        pytest.skip("a GPU is present (the run is tests/test_gpu_parity.py::test_cpp_host_api_scenes)")
+    r = subprocess.run([str(exe), str(tmp_path), "8", "8", "1"], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr  # no CPU fallback behind create_image
+
+
 def test_struct_layouts_match_ctypes(rtb):
     # sizes the Python mirror assumes (include/rtb200.h, rtb_scene_format.h)
     assert C.sizeof(rtb.RtbCamera) == 15 * 8

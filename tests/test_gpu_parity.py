@@ -334,3 +334,28 @@ def test_full_size_properties_4k(rtb, orc):
     s_lo, w_lo, cam_lo = rtb.Scene.named("final_scene_lit", 384, 216)
     ref, _, _ = orc.OracleScene(s_lo.serialize(), w_lo).render(cam_lo, 384, 216, 64, seed=3, nthreads=os.cpu_count() or 1)
     assert abs((whole / 4).mean() / ref.mean() - 1.0) < 0.03
+
+
+# ---- 10. the C++ host API (include/rtb200.hpp): the reference's #[test] bodies, tests/cpp/test_scenes.cpp ---------
+def test_cpp_host_api_scenes(rtb, tmp_path):
+    # create_image(ny, nx, ns, cam, world) -> P3 text, scenes built with the crate-shaped constructors, against the
+    # same scenes through the C ABI's rtb_scene_named: identical scene => identical paths; the order of the float
+    # adds into a pixel is not fixed, so a rare value may quantise 1 LSB apart
+    import subprocess
+    from test_cabi import build_cpp_scene_test
+    exe = build_cpp_scene_test(tmp_path)
+    nx, ny, ns = 96, 54, 8
+    r = subprocess.run([str(exe), str(tmp_path), str(nx), str(ny), str(ns)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    lines = dict((l.split()[0], l.split()[1:]) for l in r.stdout.splitlines())
+    for name, bg in (("two_spheres", rtb.BG_SKY), ("cornell_box", rtb.BG_BLACK)):
+        text = (tmp_path / f"{name}.ppm").read_text()
+        assert int(lines[name][0]) == len(text)
+        tok = text.split()
+        assert tok[:4] == ["P3", str(nx), str(ny), "255"]  # tests/test.rs:59
+        got = np.array(tok[4:], dtype=np.int64).reshape(ny, nx, 3)
+        s, w, cam = rtb.Scene.named(name, nx, ny)
+        _, ref8, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=7, background=bg))
+        d = np.abs(got - ref8.astype(np.int64))
+        assert d.max() <= 1 and (d > 0).mean() < 1e-3, (name, d.max(), (d > 0).mean())
+        assert got.max() > 0  # a lit image, not the all-black case
