@@ -266,13 +266,17 @@ def run_gpu(args):
     peaks = measured_peaks()
     prop = torch.cuda.get_device_properties(local)
     sm_mhz = ck["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)
-    issue_peak = prop.multi_processor_count * 128 * sm_mhz * 1e6 / 1e12  # T lane-instr/s at the clock seen
+    nominal_peak = prop.multi_processor_count * 128 * sm_mhz * 1e6 / 1e12  # T lane-instr/s at the clock seen
+    # calibration on this device (csrc/calib.cu): FFMA chains alone, and FFMA + LOP3 interleaved (FMA and ALU pipe both fed)
+    fma_peak, mixed_peak, slab_peak = rtb.issue_peak(local)
+    issue_peak = max(fma_peak, mixed_peak, slab_peak)
     achieved = work_per_step / (kern_ms / args.steps * 1e-3) / 1e12
     roofline = {
         "bound": "fp32_issue", "achieved": achieved, "peak": issue_peak, "unit": "Tlane-instr/s",
         "frac": achieved / issue_peak, "traffic": ncu_traffic_bytes(NX, NY, spp),
         "note": ("SURVEY.md §8(d): scene tables (<1 MB + 1.5 MB texture) stay in L1/L2, no dense contraction, so the bound is "
-                 "SM instruction issue: peak = SMs x 128 lanes x SM clock sampled during the run; achieved = algorithmic "
+                 "SM instruction issue: peak = lane-instructions/s measured on this device by an FFMA+LOP3 issue microbenchmark "
+                 "(rtb_issue_peak; nominal SMs x 128 lanes x sampled SM clock alongside); achieved = algorithmic "
                  "lane-instructions (fixed cost table x device op counters of one step) / kernel time. "
                  "MEASURED_PEAKS.json has no FP32 entry. traffic = dram bytes read + written by one launch of this "
                  "workload (ncu, profiles/r1_mega_traffic_4k64.csv): megabytes against the algorithmic image + scene "
@@ -282,6 +286,7 @@ def run_gpu(args):
         "lane_instr_per_segment_model": work_per_step / st["segments"],
         "Msegments_per_s": value * st["segments"] / st["paths"],
         "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
+        "peak_nominal": nominal_peak, "peak_measured_fma_only": fma_peak, "peak_measured_fma_lop3": mixed_peak, "peak_measured_slab_mix": slab_peak,
     }
     cpu_v, cpu_desc, cores, _ = cpu_reference_sample(seconds=args.cpu_seconds) if args.cpu_seconds > 0 else (None, "skipped", 0, 0)
     line = {

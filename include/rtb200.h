@@ -214,6 +214,12 @@ int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, in
 int rtb_render_multi(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns, const rtb_render_opts*,
                      const int* devices, int n_devices, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
 
+/* Issue-rate calibration for the roofline denominator (csrc/calib.cu): lane-instructions per second
+ * (in 10^12) the whole device sustains on FFMA chains alone and on FFMA + LOP3 chains interleaved
+ * 1:1 (both the FMA and the ALU pipe busy), and on the 1 FFMA : 2 FMNMX mix of the BVH slab test.
+ * ~0.1 s of GPU time. */
+int rtb_issue_peak(int device, double* fma_tlane_per_s, double* mixed_tlane_per_s, double* slab_tlane_per_s);
+
 /* Closest-hit query for the primitive-ID parity test: Hittable::hit(ray, t_min, f64::MAX)
  * (src/color.rs:7) with ConstantMedium objects skipped.  rays = n x {ox,oy,oz,dx,dy,dz,time}
  * (host, double); out_prim[i] = primitive ID or -1; out_t[i] = t (undefined on a miss). */

@@ -119,6 +119,7 @@ _sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
 _sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
 _sig("rtb_render_multi", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), C.POINTER(C.c_int), _i, _vp, _vp,
      C.POINTER(Stats))
+_sig("rtb_issue_peak", _i, _i, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double))
 PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_double, C.c_double)
 _sig("rtb_render_progressive", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _i, _i, PROGRESS_FN, _vp,
      _vp, _vp, C.POINTER(C.c_int))
@@ -156,6 +157,13 @@ def _h(code, where):
 
 def _vec3(v):
     return (C.c_double * 3)(*[float(x) for x in v])
+
+
+def issue_peak(device=0):
+    """(FFMA only, FFMA+LOP3 1:1, FFMA+FMNMX 1:2) lane-instructions per second in 1e12 on `device` (rtb_issue_peak)."""
+    a, b, c = C.c_double(0), C.c_double(0), C.c_double(0)
+    _h(lib.rtb_issue_peak(device, C.byref(a), C.byref(b), C.byref(c)), "issue_peak")
+    return a.value, b.value, c.value
 
 
 def device_count() -> int:
