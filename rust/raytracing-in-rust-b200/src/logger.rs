@@ -1,35 +1,35 @@
-//! A small stand-in for src/logger.rs so the driver's `Logger::new(path)` / `set_level` / `write`
-//! lines keep compiling: "<unix seconds> [LEVEL] - message" appended to the file.  (Real progress
-//! reporting is rtb_render_progressive's callback.)
-use std::fs::OpenOptions;
-use std::io::Write;
-use std::time::{SystemTime, UNIX_EPOCH};
+//! Stand-in for the reference's logger module so the driver's `Logger::new(path)`, `set_level(DEBUG)` and
+//! `write("..")` lines keep compiling.  One line per call is appended to the file:
+//! "<unix seconds> [LEVEL] - message".  (Real progress reporting is rtb_render_progressive's callback.)
+use std::fmt;
+use std::io::Write as _;
+use std::path::PathBuf;
 
-#[derive(Clone, Copy, Debug)]
 #[allow(clippy::upper_case_acronyms)]
-pub enum LogLevel {
-    INFO,
-    DEBUG,
-    WARNING,
-    ERROR,
+#[derive(Debug, Clone, Copy)]
+pub enum LogLevel { INFO, DEBUG, WARNING, ERROR }
+
+impl fmt::Display for LogLevel {
+    fn fmt(&self, f: &mut fmt::Formatter<'_>) -> fmt::Result {
+        fmt::Debug::fmt(self, f)
+    }
 }
 
-#[derive(Clone, Debug)]
-pub struct Logger {
-    level: LogLevel,
-    path: String,
-}
+#[derive(Debug, Clone)]
+pub struct Logger { file: PathBuf, tag: LogLevel }
 
 impl Logger {
     pub fn new(path: &str) -> Self {
-        Logger { level: LogLevel::DEBUG, path: path.to_owned() }
+        Logger { file: PathBuf::from(path), tag: LogLevel::DEBUG }
     }
+
     pub fn set_level(&mut self, l: LogLevel) {
-        self.level = l
+        self.tag = l;
     }
+
     pub fn write(&self, description: &str) -> std::io::Result<()> {
-        let secs = SystemTime::now().duration_since(UNIX_EPOCH).map(|d| d.as_secs()).unwrap_or(0);
-        let mut f = OpenOptions::new().append(true).create(true).open(&self.path)?;
-        writeln!(f, "{} [{:?}] - {}", secs, self.level, description)
+        let now = std::time::SystemTime::now().duration_since(std::time::UNIX_EPOCH).map_or(0, |d| d.as_secs());
+        let mut out = std::fs::OpenOptions::new().create(true).append(true).open(&self.file)?;
+        writeln!(out, "{} [{}] - {}", now, self.tag, description)
     }
 }
