@@ -51,7 +51,7 @@ extern "C" int rtb_issue_peak(int device, double* fma_tlane_per_s, double* mixed
                                     std::string("issue_peak: ") + cudaGetErrorString(e));
   int sms = 0;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-  const int blocks = sms * 8, threads = 256, iters = 1 << 16;
+  const int blocks = sms * 8, threads = 256, iters = 1 << 15;
   float* d_out = nullptr;
   if ((e = cudaMalloc(&d_out, (size_t)blocks * threads * sizeof(float))) != cudaSuccess) return cfail(e);
   cudaEvent_t e0, e1;
