@@ -248,7 +248,9 @@ def run_gpu(args):
             o2 = rtb.default_opts(pipeline=pipe, device=local, sample_begin=rank, sample_stride=world)
             # create_image returns the quantised image only (tests/test.rs:71-84): the result read back is rgb8
             g_sum, g8, _ = s2.render(w, cam, NX, NY, ns_total, o2, want_sum=False)
-            t_e2e += time.perf_counter() - t0
+            dt_call = time.perf_counter() - t0
+            t_e2e += dt_call
+            print(f"[bench] e2e call {k}: {dt_call * 1e3:.1f} ms", file=sys.stderr)
             h2d = s2.device_bytes() + 256  # scene tables + camera/params
             d2h = g8.nbytes
             del s2

@@ -206,7 +206,7 @@ class Scene:
 
     def __del__(self):
         p, self._p = getattr(self, "_p", None), None
-        if p:
+        if p and lib is not None:  # `lib` is already None when the interpreter tears the module down
             lib.rtb_scene_destroy(p)
 
     # -- textures (src/texture.rs)
