@@ -214,6 +214,9 @@ int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, in
 int rtb_render_multi(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns, const rtb_render_opts*,
                      const int* devices, int n_devices, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
 
+/* Philox4x32-10 (the renderer's counter-based generator, csrc/philox.h) on the host, for known-answer tests. */
+int rtb_philox4x32_10(const uint32_t counter[4], const uint32_t key[2], uint32_t out[4]);
+
 /* Issue-rate calibration for the roofline denominator (csrc/calib.cu): lane-instructions per second
  * (in 10^12) the whole device sustains on FFMA chains alone and on FFMA + LOP3 chains interleaved
  * 1:1 (both the FMA and the ALU pipe busy), and on the 1 FFMA : 2 FMNMX mix of the BVH slab test.

@@ -119,6 +119,7 @@ _sig("rtb_render_opts_default", None, C.POINTER(RenderOpts))
 _sig("rtb_render", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _vp, _vp, C.POINTER(Stats))
 _sig("rtb_render_multi", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), C.POINTER(C.c_int), _i, _vp, _vp,
      C.POINTER(Stats))
+_sig("rtb_philox4x32_10", _i, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))
 _sig("rtb_issue_peak", _i, _i, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double))
 PROGRESS_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint8), C.c_double, C.c_double)
 _sig("rtb_render_progressive", _i, _vp, _i, C.POINTER(RtbCamera), _i, _i, _i, C.POINTER(RenderOpts), _i, _i, PROGRESS_FN, _vp,
@@ -157,6 +158,13 @@ def _h(code, where):
 
 def _vec3(v):
     return (C.c_double * 3)(*[float(x) for x in v])
+
+
+def philox4x32_10(counter, key):
+    """One Philox4x32-10 block on the host (rtb_philox4x32_10): counter = 4 x u32, key = 2 x u32 -> 4 x u32."""
+    c, k, o = (C.c_uint32 * 4)(*counter), (C.c_uint32 * 2)(*key), (C.c_uint32 * 4)()
+    _h(lib.rtb_philox4x32_10(c, k, o), "philox4x32_10")
+    return tuple(int(x) for x in o)
 
 
 def issue_peak(device=0):

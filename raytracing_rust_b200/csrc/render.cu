@@ -786,6 +786,15 @@ int rtb_debug_texture_value(rtb_scene* s, int world, int tex, const double* uvp,
 
 // Camera::get_ray for the fixed parity batch, on the host in f64, from the same Philox draws
 // the kernels use (trace.cuh camera_ray): ray i = sample `sidx` of pixel i.
+// The counter-based generator every draw of the renderer comes from (csrc/philox.h), exposed so the published
+// known-answer vectors of Philox4x32-10 (Salmon et al., Random123 kat_vectors) can pin it.  Host code.
+int rtb_philox4x32_10(const uint32_t counter[4], const uint32_t key[2], uint32_t out[4]) {
+  if (!counter || !key || !out) return fail(RTB_ERR_INVALID, "philox4x32_10: null argument");
+  const u4 r = philox4x32_10(u4{counter[0], counter[1], counter[2], counter[3]}, key[0], key[1]);
+  out[0] = r.x, out[1] = r.y, out[2] = r.z, out[3] = r.w;
+  return RTB_OK;
+}
+
 int rtb_primary_rays(const RtbCamera* c, int nx, int ny, int sidx, uint64_t seed, double* out) {
   if (!c || !out || nx <= 0 || ny <= 0) return fail(RTB_ERR_INVALID, "primary_rays: bad argument");
   auto sub = [](const double* a, const double* b, double* r) { for (int i = 0; i < 3; ++i) r[i] = a[i] - b[i]; };

@@ -175,3 +175,15 @@ def test_primary_rays_are_deterministic_and_in_frustum(rtb):
     assert np.all((a[:, 6] >= 0) & (a[:, 6] < 1))  # time in [t0, t1)  (src/camera.rs:61)
     # lens offsets stay inside aperture/2 of the eye (src/camera.rs:57-59)
     assert np.all(np.linalg.norm(a[:, :3] - np.array([278, 278, -800.0]), axis=1) <= 0.05 + 1e-12)
+
+
+def test_philox_known_answers(rtb):
+    # Philox4x32-10 known-answer vectors published with Random123 (kat_vectors: zeros, all ones, digits of pi);
+    # every draw of the renderer is one of these blocks cut into five 24-bit uniforms (csrc/philox.h)
+    f = 0xFFFFFFFF
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8)),
+           ((f, f, f, f), (f, f), (0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD)),
+           ((0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344), (0xA4093822, 0x299F31D0),
+            (0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1))]
+    for ctr, key, want in kat:
+        assert rtb.philox4x32_10(ctr, key) == want
