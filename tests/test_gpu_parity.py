@@ -359,3 +359,12 @@ def test_cpp_host_api_scenes(rtb, tmp_path):
         d = np.abs(got - ref8.astype(np.int64))
         assert d.max() <= 1 and (d > 0).mean() < 1e-3, (name, d.max(), (d > 0).mean())
         assert got.max() > 0  # a lit image, not the all-black case
+
+
+# ---- 11. soak: random sizes / shards / pipelines / thresholds all terminate with exact path counts -----------------
+def test_random_sizes_shards_and_pipelines_terminate(rtb):
+    import subprocess
+    import sys
+    tool = Path(__file__).resolve().parent.parent / "tools" / "fuzz_sizes.py"
+    r = subprocess.run([sys.executable, str(tool), "8", "3"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "fuzz ok" in r.stdout, r.stderr[-2000:]
