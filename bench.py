@@ -99,7 +99,7 @@ def measured_peaks():
     return json.loads(p.read_text()) if p.exists() else {}
 
 
-def cpu_reference_sample(seconds=15.0, nthreads=None, seed=11):
+def cpu_reference_sample(seconds=15.0, nthreads=None, seed=11, scene_name=None, nx=480, ny=270):
     """Times the CPU oracle (f64 restatement of the reference; the Rust original cannot be built
     here) on a bounded sample of the SAME workload: final_scene, same camera, 480x270, spp sized
     for ~`seconds` of wall time on `nthreads` host threads.  Returns (Mpaths/s, description, cores)."""
@@ -107,8 +107,8 @@ def cpu_reference_sample(seconds=15.0, nthreads=None, seed=11):
     from oracle import oracle_py as orc
 
     nthreads = nthreads or os.cpu_count() or 1
-    nx, ny = 480, 270
-    s, w, cam = rtb.Scene.named(SCENE, nx, ny)
+    scene_name = scene_name or SCENE
+    s, w, cam = rtb.Scene.named(scene_name, nx, ny)
     o = orc.OracleScene(s.serialize(), w)
     t0 = time.perf_counter()
     o.render(cam, nx, ny, 1, seed=seed, nthreads=nthreads)  # calibration pass (also warms caches)
@@ -118,9 +118,36 @@ def cpu_reference_sample(seconds=15.0, nthreads=None, seed=11):
     _, _, segs = o.render(cam, nx, ny, spp, seed=seed + 1, nthreads=nthreads)
     dt = time.perf_counter() - t0
     paths = nx * ny * spp
-    desc = (f"{SCENE} {nx}x{ny} x {spp} spp = {paths / 1e6:.2f} Mpaths in {dt:.1f} s on {nthreads} threads "
+    desc = (f"{scene_name} {nx}x{ny} x {spp} spp = {paths / 1e6:.2f} Mpaths in {dt:.1f} s on {nthreads} threads "
             f"({segs / paths:.2f} segments/path); C++ f64 port of src/*.rs (oracle/oracle.cpp)")
     return paths / dt / 1e6, desc, nthreads, dt
+
+
+def run_configs_table(args):
+    """--configs-table: BASELINE.json's five configs rendered in FULL on one GPU (time-to-image measured, not
+    extrapolated), each next to the CPU oracle timed on a bounded sample of the same scene and camera (the same
+    cpu_baseline leg as the headline line).  Markdown on stdout (profiles/r1_configs.md)."""
+    import raytracing_rust_b200 as rtb
+
+    configs = [("C1", "two_spheres", 400, 225, 100), ("C2", "random_scene", 1920, 1080, 500), ("C3", "two_perlin_sphere", 1920, 1080, 1000),
+               ("C3", "earth", 1920, 1080, 1000), ("C4", "cornell_box", 1024, 1024, 10000), ("C4", "cornell_smoke", 1024, 1024, 10000),
+               ("C5", "final_scene", 3840, 2160, 10000)]
+    nth = os.cpu_count() or 1
+    print(f"| cfg | scene (as written, black background) | image | spp | paths | GPU s | GPU Mpaths/s | GPU Mseg/s | seg/path | "
+          f"CPU oracle Mpaths/s ({nth} thr) | CPU sample | speed-up |")
+    print("|---|---|---|---:|---:|---:|---:|---:|---:|---:|---|---:|")
+    for cfg, name, nx, ny, ns in configs:
+        s, w, cam = rtb.Scene.named(name, nx, ny)
+        s.render(w, cam, nx, ny, 2, want_sum=False, want_rgb8=False)
+        t0 = time.perf_counter()
+        _, _, st = s.render(w, cam, nx, ny, ns, want_sum=False, want_stats=True)
+        wall = time.perf_counter() - t0
+        cpu, desc, _, _ = cpu_reference_sample(seconds=min(args.cpu_seconds, 8.0), scene_name=name, nx=max(16, nx // 4), ny=max(16, ny // 4))
+        paths = nx * ny * ns
+        gpu = paths / (st["device_ms"] * 1e-3) / 1e6
+        print(f"| {cfg} | {name} | {nx}x{ny} | {ns} | {paths / 1e9:.3f} G | {st['device_ms'] / 1e3:.2f} (wall {wall:.2f}) | {gpu:.0f} | "
+              f"{st['segments'] / st['device_ms'] / 1e3:.0f} | {st['segments'] / st['paths']:.2f} | {cpu:.2f} | {desc.split(' on ')[0]} | "
+              f"{gpu / cpu:.0f}x |", flush=True)
 
 
 def run_reference(args):
@@ -335,8 +362,11 @@ def main():
     ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--spp-per-step", type=int, default=SPP_PER_STEP)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--configs-table", action="store_true", help="render all five BASELINE configs in full and print a markdown table")
     args = ap.parse_args()
-    if args.impl == "reference":
+    if args.configs_table:
+        run_configs_table(args)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_gpu(args)
