@@ -247,6 +247,21 @@ size_t rtb_ppm_p6(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap);
 /* File::create(path) + write!(file, "{}", create_image(..)) of the #[test] wrappers
  * (tests/test.rs:536,557): binary == 0 writes the reference's P3 text, else P6. */
 int rtb_image_write_ppm(const char* path, const uint8_t* rgb8, int nx, int ny, int binary);
+/* The same image as an 8-bit RGB PNG (zlib stored blocks; any PNG reader opens it). */
+int rtb_image_write_png(const char* path, const uint8_t* rgb8, int nx, int ny);
+
+/* ---- JPEG input: image::open(path).to_rgb8() of tests/test.rs:201-205,489-493 ---------------
+ * (upstream: crates image 0.25.1 / zune-jpeg 0.4.11, Cargo.lock:376-394,1363-1364).  Baseline and
+ * extended-sequential Huffman JPEG, 8 bit, grey or 3 components with 1x1 / 2x1 / 2x2 chroma
+ * sampling, restart intervals; integer slow IDCT, triangle chroma interpolation and fixed-point
+ * YCbCr->RGB, i.e. byte-identical to the libjpeg(-turbo) default decode (tests/test_image_io.py).
+ * *rgb8_out is malloc'ed (3*nx*ny bytes, row 0 = top) and released with rtb_image_free.
+ * Progressive / arithmetic / 12-bit files fail with RTB_ERR_INVALID; unreadable files RTB_ERR_IO. */
+int rtb_jpeg_decode(const uint8_t* data, size_t len, uint8_t** rgb8_out, uint32_t* nx, uint32_t* ny);
+int rtb_jpeg_decode_file(const char* path, uint8_t** rgb8_out, uint32_t* nx, uint32_t* ny);
+void rtb_image_free(uint8_t* rgb8);
+/* ImageTexture::new(image::open(path).to_rgb8().into_raw(), nx, ny): decode + rtb_tex_image. */
+int rtb_tex_image_file(rtb_scene*, const char* path);
 
 #ifdef __cplusplus
 }

@@ -99,6 +99,21 @@ struct NoiseTexture : Texture {  // src/texture.rs:51-72; tables drawn at constr
   }
 };
 
+// image::open(path).expect(..).to_rgb8() of tests/test.rs:201-205: the decoded pixels of a JPEG file
+struct RgbImage {
+  std::vector<uint8_t> data;
+  uint32_t nx = 0, ny = 0;
+  std::vector<uint8_t> into_raw() && { return std::move(data); }
+};
+inline RgbImage open_image(const std::string& path) {
+  uint8_t* p = nullptr;
+  RgbImage im;
+  check(rtb_jpeg_decode_file(path.c_str(), &p, &im.nx, &im.ny), "image::open");
+  im.data.assign(p, p + (size_t)3 * im.nx * im.ny);
+  rtb_image_free(p);
+  return im;
+}
+
 struct ImageTexture : Texture {  // src/texture.rs:74-108
   std::shared_ptr<const std::vector<uint8_t>> data;
   uint32_t nx, ny;

@@ -140,6 +140,11 @@ _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
 _sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
 _sig("rtb_ppm_p6", _sz, _vp, _i, _i, _vp, _sz)
 _sig("rtb_image_write_ppm", _i, C.c_char_p, _vp, _i, _i, _i)
+_sig("rtb_image_write_png", _i, C.c_char_p, _vp, _i, _i)
+_sig("rtb_jpeg_decode", _i, _vp, _sz, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))
+_sig("rtb_jpeg_decode_file", _i, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))
+_sig("rtb_image_free", None, _vp)
+_sig("rtb_tex_image_file", _i, _vp, C.c_char_p)
 _sig("rtb_scene_save", _i, _vp, C.c_char_p)
 _sig("rtb_scene_load", _vp, C.c_char_p)
 
@@ -231,6 +236,10 @@ class Scene:
         a = np.ascontiguousarray(rgb8, dtype=np.uint8)
         ny, nx = a.shape[0], a.shape[1]
         return _h(lib.rtb_tex_image(self._p, a.ctypes.data, nx, ny), "tex_image")
+
+    def image_file(self, path):
+        """ImageTexture::new(image::open(path).to_rgb8().into_raw(), nx, ny), tests/test.rs:201-205"""
+        return _h(lib.rtb_tex_image_file(self._p, str(path).encode()), "tex_image_file")
 
     # -- materials (src/material.rs)
     def lambertian(self, tex):
@@ -495,6 +504,26 @@ def write_ppm(path, rgb8: np.ndarray, binary=False):
     """File::create + write! of the reference's #[test] wrappers (tests/test.rs:536,557); P3 text or P6."""
     a = np.ascontiguousarray(rgb8, dtype=np.uint8)
     _h(lib.rtb_image_write_ppm(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0], int(bool(binary))), "image_write_ppm")
+
+
+def write_png(path, rgb8: np.ndarray):
+    a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    _h(lib.rtb_image_write_png(str(path).encode(), a.ctypes.data, a.shape[1], a.shape[0]), "image_write_png")
+
+
+def decode_jpeg(src) -> np.ndarray:
+    """image::open(path).to_rgb8() (tests/test.rs:201-205): `src` is a path or the file's bytes; (ny, nx, 3) uint8."""
+    out, nx, ny = C.c_void_p(), C.c_uint32(), C.c_uint32()
+    if isinstance(src, (bytes, bytearray, memoryview)):
+        b = bytes(src)
+        _h(lib.rtb_jpeg_decode(b, len(b), C.byref(out), C.byref(nx), C.byref(ny)), "jpeg_decode")
+    else:
+        _h(lib.rtb_jpeg_decode_file(str(src).encode(), C.byref(out), C.byref(nx), C.byref(ny)), "jpeg_decode_file")
+    try:
+        a = np.ctypeslib.as_array(C.cast(out, C.POINTER(C.c_uint8)), shape=(ny.value, nx.value, 3)).copy()
+    finally:
+        lib.rtb_image_free(out)
+    return a
 
 
 def create_image(ny, nx, ns, cam, scene: Scene, world: int, opts=None) -> bytes:

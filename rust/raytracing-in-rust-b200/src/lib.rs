@@ -13,6 +13,7 @@ pub mod bvh;
 pub mod camera;
 pub mod cube;
 pub mod hittable;
+pub mod image;
 pub mod logger;
 pub mod material;
 pub mod medium;

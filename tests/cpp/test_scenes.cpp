@@ -60,6 +60,16 @@ int main(int argc, char** argv) {
       Camera cam = set_camera(nx, ny, Vector3(278, 278, -800), Vector3(278, 278, 0), up, 40.0, 10.0, 0.1, 0.0, 1.0);
       emit(dir, "cornell_box", create_image(ny, nx, ns, cam, world, &o, n_gpus));
     }
+    if (argc > 6) {  // test_earth, tests/test.rs:613-649 (scene :200-209): a bare Sphere with a JPEG ImageTexture, sky on
+      RgbImage image = open_image(argv[6]);  // image::open("texture/earthmap.jpg").expect(..).to_rgb8()
+      const uint32_t inx = image.nx, iny = image.ny;
+      ImageTexture texture(std::move(image).into_raw(), inx, iny);
+      Sphere earth(Vector3(0.0, 0.0, 0.0), 2.0, Lambertian(texture));
+      Camera cam = set_camera(nx, ny, Vector3(13, 2, 3), Vector3(0, 0, 0), up, 20.0, 10.0, 0.0, 0.0, 1.0);
+      rtb_render_opts sky = o;
+      sky.background = RTB_BG_SKY;
+      emit(dir, "earth", create_image(ny, nx, ns, cam, earth, &sky, n_gpus));
+    }
   } catch (const std::exception& e) {
     std::fprintf(stderr, "error: %s\n", e.what());
     return 1;

@@ -361,6 +361,30 @@ def test_cpp_host_api_scenes(rtb, tmp_path):
         assert got.max() > 0  # a lit image, not the all-black case
 
 
+def test_cpp_earth_scene_from_a_jpeg_file(rtb, tmp_path):
+    # tests/test.rs:200-209: image::open(..).to_rgb8() -> ImageTexture -> bare Sphere, through the C++ host API and the
+    # library's own JPEG decoder, against the same scene built here from the same decoded bytes
+    import subprocess
+    Image = pytest.importorskip("PIL.Image")
+    from test_cabi import build_cpp_scene_test
+    exe = build_cpp_scene_test(tmp_path)
+    jpg = tmp_path / "earth_small.jpg"
+    Image.fromarray(rtb.earth_rgb8()[::4, ::4].copy()).save(jpg, "JPEG", quality=92, subsampling=2)
+    tex = rtb.decode_jpeg(jpg)
+    assert np.array_equal(tex, np.asarray(Image.open(jpg).convert("RGB")))
+    nx, ny, ns = 96, 54, 8
+    r = subprocess.run([str(exe), str(tmp_path), str(nx), str(ny), str(ns), "1", str(jpg)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    got = np.array((tmp_path / "earth.ppm").read_text().split()[4:], dtype=np.int64).reshape(ny, nx, 3)
+    s = rtb.Scene()
+    w = s.sphere((0, 0, 0), 2.0, s.lambertian(s.image(tex)))
+    cam = rtb.camera((13, 2, 3), (0, 0, 0), (0, 1, 0), 20.0, nx / ny, 0.0, 10.0, 0.0, 1.0)
+    _, ref8, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=7, background=rtb.BG_SKY))
+    d = np.abs(got - ref8.astype(np.int64))
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3, (d.max(), (d > 0).mean())
+    assert got.std() > 10  # the textured sphere is in the picture
+
+
 # ---- 11. soak: random sizes / shards / pipelines / thresholds all terminate with exact path counts -----------------
 def test_random_sizes_shards_and_pipelines_terminate(rtb):
     import subprocess
