@@ -157,6 +157,9 @@ void rtb_render_opts_default(rtb_render_opts*);
  *                 (only meaningful when the call renders all ns samples) */
 int rtb_render(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns,
                const rtb_render_opts*, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
+/* rtb_render keeps its device accumulation / rgb8 buffers per device between calls (grow-only; a 4K image:
+ * 124 MB).  This frees the ones not in use.  Always RTB_OK. */
+int rtb_release_workspace(void);
 
 /* create_image in chunks of `chunk_spp` samples with real progress reporting (in place of the
  * reference's dead src/progressbar.rs and the start/end lines of src/logger.rs): after every chunk

@@ -140,6 +140,7 @@ _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
 _sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
 _sig("rtb_ppm_p6", _sz, _vp, _i, _i, _vp, _sz)
 _sig("rtb_image_write_ppm", _i, C.c_char_p, _vp, _i, _i, _i)
+_sig("rtb_release_workspace", _i)
 _sig("rtb_image_write_png", _i, C.c_char_p, _vp, _i, _i)
 _sig("rtb_jpeg_decode", _i, _vp, _sz, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))
 _sig("rtb_jpeg_decode_file", _i, C.c_char_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32))

@@ -17,10 +17,14 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -345,6 +349,20 @@ __global__ void k_texture_eval(SceneView sv, int tex, const float* __restrict__ 
                   std::string(#expr) + ": " + cudaGetErrorString(e_));                          \
   } while (0)
 
+// RTB200_TIMING=1: host wall-clock of the stages of the host-buffer call, to stderr (tools/e2e_breakdown.py)
+struct StageTimer {
+  bool on;
+  std::chrono::steady_clock::time_point t;
+  const char* what;
+  explicit StageTimer(const char* w) : on(std::getenv("RTB200_TIMING") != nullptr), t(std::chrono::steady_clock::now()), what(w) {}
+  void lap(const char* stage) {
+    if (!on) return;
+    auto n = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[rtb200 timing] %s: %s %.3f ms\n", what, stage, std::chrono::duration<double, std::milli>(n - t).count());
+    t = n;
+  }
+};
+
 void destroy_device_scene(DeviceScene* d) {
   if (!d) return;
   int prev = 0;
@@ -384,6 +402,7 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
     destroy_device_scene(s->dev);
     s->dev = nullptr;
   }
+  StageTimer tm("upload");
   DeviceScene* d = new DeviceScene();
   d->device = device;
   // who builds the BVH: the host's full-sweep SAH (best trees; O(n log^2 n)) or the device LBVH (bvh_build.cu)
@@ -394,7 +413,9 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
     delete d;
     return rc;
   }
+  tm.lap("flatten + host BVH");
   CUDA_TRY(cudaSetDevice(device));
+  tm.lap("cudaSetDevice");
   SceneView& v = d->view;
   const FlatScene& f = d->flat;
   const bool device_bvh = f.root < 0;  // flatten left the tree to the device builder
@@ -414,6 +435,7 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
     destroy_device_scene(d);
     return rc;
   }
+  tm.lap("table uploads");
   if (!device_bvh) v.n_nodes = (int)f.nodes.size(), d->n_nodes_device = v.n_nodes;
   v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
   v.root = f.root;
@@ -425,7 +447,10 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   CUDA_TRY(cudaMalloc(&wk, 64));
   d->allocs.push_back(wk);
   d->d_work = (unsigned int*)wk;
-  CUDA_TRY(cudaGetDeviceProperties(&d->prop, device));
+  tm.lap("small allocs");
+  // only the SM count is used; cudaGetDeviceProperties costs 2-4 ms per call
+  CUDA_TRY(cudaDeviceGetAttribute(&d->prop.multiProcessorCount, cudaDevAttrMultiProcessorCount, device));
+  tm.lap("device attributes");
   s->dev = d;
   s->dev_world = world;
   if (std::getenv("RTB200_DEBUG"))
@@ -627,40 +652,146 @@ int rtb_resolve_device(const float* d_sum_rgb, int nx, int ny, int ns, uint8_t* 
   return RTB_OK;
 }
 
+namespace {
+// Accumulation / rgb8 buffers of the host-buffer calls are kept per device between calls (grow-only):
+// cudaMalloc + cudaFree of the 100 MB accumulator of a 4K image cost 2-6 ms per call otherwise.
+// A second concurrent render on the same device gets private buffers.  rtb_release_workspace() frees them.
+struct Workspace {
+  void* sum = nullptr;
+  size_t sum_bytes = 0;
+  void* rgb = nullptr;
+  size_t rgb_bytes = 0;
+  bool busy = false;
+};
+std::mutex g_ws_mutex;
+std::map<int, Workspace> g_ws;
+
+struct WorkspaceLease {
+  int device;
+  float* d_sum = nullptr;
+  uint8_t* d_rgb8 = nullptr;
+  bool cached = false;
+  ~WorkspaceLease() {
+    if (cached) {
+      std::lock_guard<std::mutex> lk(g_ws_mutex);
+      g_ws[device].busy = false;
+    } else {
+      if (d_sum) cudaFree(d_sum);
+      if (d_rgb8) cudaFree(d_rgb8);
+    }
+  }
+};
+
+cudaError_t lease_workspace(int device, size_t sum_bytes, size_t rgb_bytes, WorkspaceLease* L) {
+  L->device = device;
+  std::lock_guard<std::mutex> lk(g_ws_mutex);
+  Workspace& w = g_ws[device];
+  cudaError_t e;
+  if (w.busy) {
+    if ((e = cudaMalloc((void**)&L->d_sum, sum_bytes)) != cudaSuccess) return e;
+    if (rgb_bytes && (e = cudaMalloc((void**)&L->d_rgb8, rgb_bytes)) != cudaSuccess) return e;
+    return cudaSuccess;
+  }
+  if (w.sum_bytes < sum_bytes) {
+    if (w.sum) cudaFree(w.sum);
+    w.sum = nullptr, w.sum_bytes = 0;
+    if ((e = cudaMalloc(&w.sum, sum_bytes)) != cudaSuccess) return e;
+    w.sum_bytes = sum_bytes;
+  }
+  if (w.rgb_bytes < rgb_bytes) {
+    if (w.rgb) cudaFree(w.rgb);
+    w.rgb = nullptr, w.rgb_bytes = 0;
+    if ((e = cudaMalloc(&w.rgb, rgb_bytes)) != cudaSuccess) return e;
+    w.rgb_bytes = rgb_bytes;
+  }
+  w.busy = true;
+  L->cached = true, L->d_sum = (float*)w.sum, L->d_rgb8 = rgb_bytes ? (uint8_t*)w.rgb : nullptr;
+  return cudaSuccess;
+}
+
+// While the GPU renders, the host thread would only wait: a helper touches every page of the caller's output
+// buffer (a fresh allocation faults page by page inside the D2H copy otherwise: 4K rgb8, 6 ms instead of 1)
+// and pins it, so the copy at the end is one DMA at full PCIe rate.
+struct OutputStager {
+  std::thread th;
+  bool pinned = false;
+  void* ptr = nullptr;
+  void start(int device, void* p, size_t bytes) {
+    ptr = p;
+    th = std::thread([this, device, p, bytes]() {
+      volatile uint8_t* b = (volatile uint8_t*)p;
+      for (size_t i = 0; i < bytes; i += 4096) b[i] = 0;
+      if (bytes) b[bytes - 1] = 0;
+      if (cudaSetDevice(device) == cudaSuccess && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned = true;
+      else cudaGetLastError();
+    });
+  }
+  void join() {
+    if (th.joinable()) th.join();
+  }
+  ~OutputStager() {
+    join();
+    if (pinned) cudaHostUnregister(ptr);
+  }
+};
+}  // namespace
+
+int rtb_release_workspace(void) {
+  std::lock_guard<std::mutex> lk(g_ws_mutex);
+  int prev = 0;
+  cudaGetDevice(&prev);
+  for (auto& kv : g_ws) {
+    if (kv.second.busy) continue;
+    cudaSetDevice(kv.first);
+    if (kv.second.sum) cudaFree(kv.second.sum);
+    if (kv.second.rgb) cudaFree(kv.second.rgb);
+    kv.second = Workspace();
+  }
+  cudaSetDevice(prev);
+  return RTB_OK;
+}
+
 int rtb_render(rtb_scene* s, int world, const RtbCamera* camera, int nx, int ny, int ns, const rtb_render_opts* opts,
                float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats* stats) {
   if (!s || !camera || nx <= 0 || ny <= 0 || ns <= 0) return fail(RTB_ERR_INVALID, "render: bad argument");
   rtb_render_opts o;
   if (opts) o = *opts; else rtb_render_opts_default(&o);
+  StageTimer tm("render");
   int rc = ensure_uploaded(s, world, o.device, std::min(camera->time0, camera->time1), std::max(camera->time0, camera->time1));
   if (rc != RTB_OK) return rc;
+  tm.lap("ensure_uploaded");
   CUDA_TRY(cudaSetDevice(o.device));
   const size_t n = (size_t)3 * nx * ny;
-  float* d_sum = nullptr;
-  uint8_t* d_rgb8 = nullptr;
-  CUDA_TRY(cudaMalloc(&d_sum, n * sizeof(float)));
-  auto cleanup = [&]() {
-    cudaFree(d_sum);
-    if (d_rgb8) cudaFree(d_rgb8);
-  };
-  cudaError_t e = cudaMemsetAsync(d_sum, 0, n * sizeof(float), 0);
-  if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+  WorkspaceLease ws;
+  cudaError_t e = lease_workspace(o.device, n * sizeof(float), out_rgb8 ? n : 0, &ws);
+  if (e != cudaSuccess) return fail(RTB_ERR_CUDA, std::string("render: device buffers: ") + cudaGetErrorString(e));
+  float* d_sum = ws.d_sum;
+  uint8_t* d_rgb8 = ws.d_rgb8;
+  e = cudaMemsetAsync(d_sum, 0, n * sizeof(float), 0);
+  if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
+  OutputStager stage_rgb8, stage_sum;  // joined (and unpinned) on every return path
+  const size_t stage_min = (size_t)1 << 20;  // not worth a thread for small images
+  if (out_rgb8 && n >= stage_min) stage_rgb8.start(o.device, out_rgb8, n);
+  if (out_sum_rgb && n * sizeof(float) >= stage_min) stage_sum.start(o.device, out_sum_rgb, n * sizeof(float));
+  tm.lap("device buffers + memset (async)");
   rc = rtb_render_device(s, camera, nx, ny, ns, &o, d_sum, nullptr, stats);
-  if (rc != RTB_OK) { cleanup(); return rc; }
+  if (rc != RTB_OK) return rc;
+  tm.lap("render_device (launch; waits only with stats)");
   if (out_rgb8) {
-    e = cudaMalloc(&d_rgb8, n);
-    if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
     rc = rtb_resolve_device(d_sum, nx, ny, ns, d_rgb8, nullptr);
-    if (rc != RTB_OK) { cleanup(); return rc; }
+    if (rc != RTB_OK) return rc;
+    stage_rgb8.join();
     e = cudaMemcpy(out_rgb8, d_rgb8, n, cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+    if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
+    tm.lap("resolve + D2H rgb8 (includes waiting for the render)");
   }
   if (out_sum_rgb) {
+    stage_sum.join();
     e = cudaMemcpy(out_sum_rgb, d_sum, n * sizeof(float), cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) { cleanup(); return fail(RTB_ERR_CUDA, cudaGetErrorString(e)); }
+    if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
   }
   e = cudaDeviceSynchronize();
-  cleanup();
+  tm.lap("sync");
   if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
   return RTB_OK;
 }

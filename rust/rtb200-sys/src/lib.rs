@@ -116,6 +116,7 @@ extern "C" {
     pub fn rtb_ppm_p3(rgb8: *const u8, nx: c_int, ny: c_int, out: *mut c_char, cap: usize) -> usize;
     pub fn rtb_ppm_p6(rgb8: *const u8, nx: c_int, ny: c_int, out: *mut c_char, cap: usize) -> usize;
     pub fn rtb_image_write_ppm(path: *const c_char, rgb8: *const u8, nx: c_int, ny: c_int, binary: c_int) -> c_int;
+    pub fn rtb_release_workspace() -> c_int;
     pub fn rtb_image_write_png(path: *const c_char, rgb8: *const u8, nx: c_int, ny: c_int) -> c_int;
     // JPEG input: image::open(path).to_rgb8(), tests/test.rs:201-205 (replaces the `image` crate dependency)
     pub fn rtb_jpeg_decode(data: *const u8, len: usize, rgb8_out: *mut *mut u8, nx: *mut u32, ny: *mut u32) -> c_int;
