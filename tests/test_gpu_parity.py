@@ -392,3 +392,47 @@ def test_random_sizes_shards_and_pipelines_terminate(rtb):
     tool = Path(__file__).resolve().parent.parent / "tools" / "fuzz_sizes.py"
     r = subprocess.run([sys.executable, str(tool), "8", "3"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "fuzz ok" in r.stdout, r.stderr[-2000:]
+
+
+# ---- 12. host-buffer call plumbing: cached device workspace, pinned output staging, concurrent callers --------------
+def test_concurrent_host_calls_share_one_device_correctly(rtb):
+    # rtb_render keeps its accumulator per device between calls and stages the caller's buffers from a helper thread:
+    # calls of different sizes interleaved from several host threads must return exactly what they return alone
+    import threading
+
+    jobs = [("cornell_box", 700, 640, 3, rtb.BG_BLACK), ("two_spheres", 801, 450, 2, rtb.BG_SKY),
+            ("final_scene_lit", 960, 540, 2, rtb.BG_BLACK), ("random_scene", 333, 777, 2, rtb.BG_SKY)]
+
+    def run(job):
+        name, nx, ny, ns, bg = job
+        s, w, cam = rtb.Scene.named(name, nx, ny)
+        a, r8, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=11, background=bg))
+        return a, r8
+
+    alone = [run(j) for j in jobs]
+    assert rtb.lib.rtb_release_workspace() == 0  # the next calls allocate afresh
+    for rnd in range(3):
+        out = [None] * len(jobs)
+        th = [threading.Thread(target=lambda k=k: out.__setitem__(k, run(jobs[k]))) for k in range(len(jobs))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        for (a0, r0), (a1, r1), job in zip(alone, out, jobs):
+            # the same paths; only the order of the float adds into a pixel is free
+            assert a1.shape == a0.shape and np.allclose(a1, a0, rtol=1e-4, atol=1e-5), job
+            d = np.abs(r1.astype(int) - r0.astype(int))
+            assert d.max() <= 1 and (d > 0).mean() < 1e-3, job
+    # a caller-pinned output buffer (already registered) is accepted as well
+    import torch
+    nx, ny = 640, 600
+    s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
+    pinned = torch.empty((ny, nx, 3), dtype=torch.uint8).pin_memory()
+    buf = pinned.numpy()
+    o = rtb.default_opts(seed=3)
+    import ctypes
+    rc = rtb.lib.rtb_render(s._p, w, ctypes.byref(cam), nx, ny, 2, ctypes.byref(o), None, buf.ctypes.data, None)
+    assert rc == 0
+    _, r8, _ = s.render(w, cam, nx, ny, 2, o, want_sum=False)
+    d = np.abs(buf.astype(int) - r8.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3
