@@ -69,6 +69,14 @@ __device__ __forceinline__ int pop_live(const int* stack, const float* stack_tn,
 }
 #endif
 
+// threadIdx.x read where it is used: a volatile read cannot be hoisted, so the shared-memory addresses derived from it are
+// formed inside the SHADE / item-fetch blocks that use them instead of once per scheduler round
+__device__ __forceinline__ int tid_here() {
+  int t;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(t));
+  return t;
+}
+
 template <bool kStats, int kThreads, int kMinBlocks>
 __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
                                                         unsigned long long* __restrict__ stats,
@@ -105,9 +113,12 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
   // Path state only the SHADE phase touches is parked in shared memory (s_cold[word][thread],
   // conflict-free) so the traversal loops do not carry it in registers or spill around it.
   __shared__ float s_cold[7][256];
-#define COLD_F(w) s_cold[w][threadIdx.x]
-#define COLD_I(w) reinterpret_cast<int*>(s_cold[w])[threadIdx.x]
-  COLD_I(6) = 0;  // pix_local
+#define COLD_F(w) s_cold[w][tid]
+#define COLD_I(w) reinterpret_cast<int*>(s_cold[w])[tid]
+  {
+    const int tid = threadIdx.x;
+    COLD_I(6) = 0;  // pix_local
+  }
   int self_prim = -1, self_face = 0;
   int stack[RTB_STACK_DEPTH];
 #if RTB_STACK_TN
@@ -116,6 +127,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
   int sp = 0;
   int cur = CUR_WAIT;
   bool items_left = true;
+  bool check_wait = true;  // warp-uniform
 
   // Scheduler: NODE runs (repeatedly) while >= k_node lanes sit at inner nodes; otherwise LEAF once
   // >= k_leaf lanes hold a leaf, otherwise SHADE once >= k_shade lanes wait for it; when no
@@ -141,10 +153,14 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
       }
       m_node = __ballot_sync(0xffffffffu, cur >= 0);
     }
+    // waiting lanes can only be released (and new ones only appear) after a SHADE round: test then, not every round
+    if (check_wait) {
+    check_wait = false;
     const unsigned m_wait = __ballot_sync(0xffffffffu, cur == CUR_WAIT);
     if (m_wait != 0u) {
       // the current item is used up.  Its tile partner (the previous item) must have drained
       // before that tile can be flushed and reused for the next item.
+      const int tid = tid_here(), wib = tid >> 5;
       const int g = s_gen[wib];
       const bool alive = cur != CUR_DONE && cur != CUR_WAIT && cur != CUR_NEW;
       const unsigned m_old = __ballot_sync(0xffffffffu, alive && (COLD_I(6) >> 5) != g);
@@ -174,6 +190,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
         if (cur == CUR_WAIT) cur = items_left ? CUR_NEW : CUR_DONE;
       }
     }
+    }
     const unsigned m_leaf = __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
     const unsigned m_shade = __ballot_sync(0xffffffffu, cur == CUR_SHADE || cur == CUR_NEW);
     if ((m_node | m_leaf | m_shade) == 0u) break;  // (a waiting lane implies a live one, handled above)
@@ -187,6 +204,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
       // ------------------------------------------------------------------ SHADE phase
       if (cur == CUR_SHADE || cur == CUR_NEW) {
         bool need_new = cur == CUR_NEW;
+        const int tid = tid_here(), wib = tid >> 5;
         V3f thr = mk(COLD_F(0), COLD_F(1), COLD_F(2));
         uint32_t pixel = (uint32_t)COLD_I(3), sample = (uint32_t)COLD_I(4);
         int depth = COLD_I(5), pix_local = COLD_I(6);
@@ -279,6 +297,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           cur = sv.root;
         }
       }
+      check_wait = true;
     } else if (phase == 0) {
       if (cur >= 0) {  // below-threshold NODE step
         if (kStats) cnt.node_tests++;
