@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kDualThreads, kMinBlocks)
           best.t = SL_F(W_BT, a), best.prim = SL_I(W_BPRIM, a), best.id = SL_I(W_BID, a);
           best.face = SL_I(W_FACES, a) & 15;
           n_segments++;
-          const Rand5 rnd = rand5(P.seed, (uint32_t)depth, pixel, sample, RTB_RNG_BOUNCE);
+          const Rand5 rnd = rand5(P.keys, (uint32_t)depth, pixel, sample, RTB_RNG_BOUNCE);
           int medium = -1;
           if (sv.n_media > 0)
             medium = sample_media<kStats>(sv, ray, P.t_min, &best.t, rnd.d, rnd.e, P.seed, pixel, sample, (uint32_t)depth,
@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(kDualThreads, kMinBlocks)
             sample = (uint32_t)(P.sample_first + k * P.sample_step);
             const int i = info.x + lx, row = info.y + ly;  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
             pixel = (uint32_t)(row * P.nx + i);
-            ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.seed, pixel, sample);
+            ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.keys, pixel, sample);
             thr = mk(1.f, 1.f, 1.f);
             depth = 0, self_prim = -1, self_face = 0;
             SL_I(W_PIXEL, a) = (int)pixel, SL_I(W_SAMPLE, a) = (int)sample, SL_I(W_PIXLOCAL, a) = pix_local;
@@ -369,6 +369,7 @@ int launch_dual(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, cons
     int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
+    P.keys = philox_keys(o.seed);
     P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 12;
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 12;
     P.k_shade = o.reserved[2] > 0 ? o.reserved[2] : 12;

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "philox.h"
+
 namespace rtb {
 
 struct MegaParams {
@@ -19,6 +21,7 @@ struct MegaParams {
   int background;
   int k_node, k_leaf, k_shade;  // lanes a phase needs before the warp's scheduler runs it
   uint64_t seed;
+  PhiloxKeys keys;  // philox_keys(seed)
 };
 
 __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {

@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           // the segment's closest surface hit is in `best`; media may pre-empt it
           n_segments++;
           // all draws of this bounce: ball / schlick (a,b,c) and the first two media (d,e)
-          const Rand5 rnd = rand5(P.seed, (uint32_t)depth, pixel, sample, RTB_RNG_BOUNCE);
+          const Rand5 rnd = rand5(P.keys, (uint32_t)depth, pixel, sample, RTB_RNG_BOUNCE);
           int medium = -1;
           if (sv.n_media > 0)
             medium = sample_media<kStats>(sv, ray, P.t_min, &best.t, rnd.d, rnd.e, P.seed, pixel, sample, (uint32_t)depth,
@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             sample = (uint32_t)(P.sample_first + k * P.sample_step);
             const int i = info.x + lx, row = info.y + ly;  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
             pixel = (uint32_t)(row * P.nx + i);
-            ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.seed, pixel, sample);
+            ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.keys, pixel, sample);
             thr = mk(1.f, 1.f, 1.f);
             depth = 0, self_prim = -1, self_face = 0;
           } else {
@@ -566,6 +566,7 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
+    P.keys = philox_keys(o.seed);
     // tuning knobs (opts.reserved[0..3]); defaults from the sweep in profiles/r1_mega_sweep.txt
     P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 4;
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;

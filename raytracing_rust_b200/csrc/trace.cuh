@@ -707,7 +707,8 @@ __device__ __forceinline__ bool scatter_dir(int mat_type, float mat_param, const
 // the uniform unit disk (r = sqrt(xi), phi = 2 pi xi) — same distribution as the rejection loop
 // at src/util.rs:15-24; skipped iff lens_radius == 0 (src/camera.rs:54).  The time draw always
 // happens, as upstream (src/camera.rs:61).
-__device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, uint64_t seed, uint32_t pixel,
+template <class Seed>  // uint64_t seed, or the PhiloxKeys made from it
+__device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, const Seed& seed, uint32_t pixel,
                                            uint32_t sample) {
   const Rand5 r5 = rand5(seed, 0u, pixel, sample, RTB_RNG_CAMERA);
   const float ju = r5.a, jv = r5.b, lr = r5.c, lp = r5.d, xt = r5.e;
