@@ -8,7 +8,8 @@
 // which makes an image independent of how samples are sharded over GPUs and needs no RNG state
 // in the path.  One 128-bit Philox output is cut into FIVE 24-bit uniforms (the top 24 bits of
 // each word, plus the four low bytes of x,y,z): enough for one whole camera sample or one
-// whole bounce.  U(0,1) = (k + 0.5) * 2^-24, strictly inside (0,1).
+// whole bounce.  U = fl((k + 0.5) * 2^-24) in (0, 1]: never 0 (no log(0), no zero-length ball sample); the single
+// value k = 2^24 - 1 rounds to exactly 1.0f.
 #pragma once
 #include <stdint.h>
 
@@ -78,7 +79,15 @@ struct Rand5 {
   float a, b, c, d, e;
 };
 
-RTB_HD inline float u24_to_unit(uint32_t k) { return ((float)k + 0.5f) * (1.0f / 16777216.0f); }
+// (k + 0.5) * 2^-24 as one FMA: k * 2^-24 is exact and the single rounding of the sum is the rounding of k + 0.5 scaled
+// by a power of two, so the value is the same as the two-step form on host and device alike
+RTB_HD inline float u24_to_unit(uint32_t k) {
+#if defined(__CUDA_ARCH__)
+  return __fmaf_rn((float)k, 1.0f / 16777216.0f, 0.5f / 16777216.0f);
+#else
+  return ((float)k + 0.5f) * (1.0f / 16777216.0f);
+#endif
+}
 
 RTB_HD inline Rand5 rand5_from(const u4 r) {
   Rand5 o;

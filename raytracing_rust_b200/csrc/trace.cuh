@@ -81,7 +81,7 @@ __device__ __forceinline__ float sin_reduced(float x) {
 // (jitter_u, jitter_v, lens_r, lens_phi), block 1 = (time,-,-,-); purpose 1: block = depth,
 // the scatter draws of that bounce (ball x3, schlick); purpose 2 + g: block = depth, the
 // free-flight draws of media 4g .. 4g+3 on that segment.
-// (Rand5 / rand5 live in philox.h: five 24-bit uniforms per Philox call, strictly inside (0,1),
+// (Rand5 / rand5 live in philox.h: five 24-bit uniforms per Philox call, in (0,1] and never 0,
 // so there is no zero-length ball sample and no log(0).)
 
 // uniform in the unit ball == the distribution of the rejection loop at src/util.rs:4-13,
