@@ -22,6 +22,12 @@ struct MegaParams {
   int k_node, k_leaf, k_shade;  // lanes a phase needs before the warp's scheduler runs it
   uint64_t seed;
   PhiloxKeys keys;  // philox_keys(seed)
+  // Scenes whose (at most two) constant media are all bounded by one static sphere carry the media in the kernel
+  // parameters: centre.xyz, radius | -(1/density), material.  n_const_media = -1: use the tables (sample_media).
+  int n_const_media;
+  float4 cmedia_sphere[2];
+  float cmedia_neg_inv_density[2];
+  int cmedia_mat[2];
 };
 
 __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {

@@ -69,6 +69,42 @@ __device__ __forceinline__ int pop_live(const int* stack, const float* stack_tn,
 }
 #endif
 
+// sample_media (trace.cuh) for media held in the kernel parameters: the same arithmetic as its sphere-boundary branch,
+// with the boundary, density and draw of each medium read from the constant bank instead of three dependent loads.
+template <bool kStats>
+__device__ __forceinline__ int sample_media_const(const MegaParams& P, const RayF& ray, float* t_closest, float xi0, float xi1,
+                                                  Counters* cnt) {
+  int which = -1;
+  const float a = dot(ray.d, ray.d);
+  const float inv_a = rcp_fast(a);
+  const float inv_len = rsqrt_fast(a);
+  const float len = a * inv_len;
+#pragma unroll
+  for (int mi = 0; mi < 2; ++mi) {
+    if (mi >= P.n_const_media) break;
+    if (kStats) cnt->medium_tests++, cnt->prim_tests += 2;
+    const float4 S = P.cmedia_sphere[mi];
+    const V3f oc = ray.o - mk(S.x, S.y, S.z);
+    const float tc = -dot(oc, ray.d) * inv_a;
+    const V3f l = madd(tc, ray.d, oc);
+    const float disc = fmaf(S.w, S.w, -dot(l, l));
+    const float h = sqrt_fast(fmaxf(disc, 0.0f) * inv_a);
+    float t1 = tc - h, t2 = tc + h;
+    if (!(disc > 0.0f && t2 > t1 + 0.0001f)) continue;
+    if (t1 < P.t_min) t1 = P.t_min;
+    if (t2 > *t_closest) t2 = *t_closest;
+    if (t1 < t2) {
+      const float distance_inside = (t2 - t1) * len;
+      const float hit_distance = P.cmedia_neg_inv_density[mi] * __logf(mi == 0 ? xi0 : xi1);
+      if (hit_distance < distance_inside) {
+        *t_closest = fmaf(hit_distance, inv_len, t1);
+        which = mi;
+      }
+    }
+  }
+  return which;
+}
+
 // threadIdx.x read where it is used: a volatile read cannot be hoisted, so the shared-memory addresses derived from it are
 // formed inside the SHADE / item-fetch blocks that use them instead of once per scheduler round
 __device__ __forceinline__ int tid_here() {
@@ -214,7 +250,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           // all draws of this bounce: ball / schlick (a,b,c) and the first two media (d,e)
           const Rand5 rnd = rand5(P.keys, (uint32_t)depth, pixel, sample, RTB_RNG_BOUNCE);
           int medium = -1;
-          if (sv.n_media > 0)
+          if (P.n_const_media >= 0)
+            medium = sample_media_const<kStats>(P, ray, &best.t, rnd.d, rnd.e, &cnt);
+          else if (sv.n_media > 0)
             medium = sample_media<kStats>(sv, ray, P.t_min, &best.t, rnd.d, rnd.e, P.seed, pixel, sample, (uint32_t)depth,
                                           &cnt);
           bool ended = true;
@@ -225,7 +263,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
               s.p = madd(best.t, ray.d, ray.o);
               s.n = mk(1.f, 0.f, 0.f);
               s.u = 0.f, s.v = 0.f;
-              s.mat = __ldg(&sv.media[medium].mat);
+              s.mat = P.n_const_media >= 0 ? (medium == 0 ? P.cmedia_mat[0] : P.cmedia_mat[1]) : __ldg(&sv.media[medium].mat);
               self_prim = -1;
             } else {
               s = finalize_hit(sv, sv.prims, ray, best);
@@ -567,6 +605,21 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
     P.keys = philox_keys(o.seed);
+    {  // media into the kernel parameters when all of them (<= 2) are bounded by one static sphere
+      const FlatScene& f = d->flat;
+      P.n_const_media = f.media.size() <= 2 ? (int)f.media.size() : -1;
+      for (size_t mi = 0; mi < f.media.size() && P.n_const_media >= 0; ++mi) {
+        const DMedium& m = f.media[mi];
+        const DPrim& b = f.bprims[m.first];
+        if (m.count != 1 || RTB_PRIM_TYPE(b.c.x) != DP_SPHERE) {
+          P.n_const_media = -1;
+          break;
+        }
+        P.cmedia_sphere[mi] = make_float4(b.a.x, b.a.y, b.a.z, b.a.w);
+        P.cmedia_neg_inv_density[mi] = m.neg_inv_density;
+        P.cmedia_mat[mi] = m.mat;
+      }
+    }
     // tuning knobs (opts.reserved[0..3]); defaults from the sweep in profiles/r1_mega_sweep.txt
     P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 4;
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;
