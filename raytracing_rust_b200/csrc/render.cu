@@ -259,17 +259,18 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           V3f rad = mk(0.f, 0.f, 0.f);  // radiance this hit adds: thr * emitted (or background)
           if (medium >= 0 || best.prim >= 0) {
             Surface s;
+            int4 m;  // DMaterial: type, texture, parameter, needs_uv
             if (medium >= 0) {  // src/medium.rs:44-51
               s.p = madd(best.t, ray.d, ray.o);
               s.n = mk(1.f, 0.f, 0.f);
               s.u = 0.f, s.v = 0.f;
               s.mat = P.n_const_media >= 0 ? (medium == 0 ? P.cmedia_mat[0] : P.cmedia_mat[1]) : __ldg(&sv.media[medium].mat);
+              m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
               self_prim = -1;
             } else {
-              s = finalize_hit(sv, sv.prims, ray, best);
+              s = finalize_hit(sv, sv.prims, ray, best, &m);
               self_prim = best.prim, self_face = best.face;
             }
-            const int4 m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
             if (kStats) n_shade[m.x]++;
             // the material's one texture lookup: emitted colour of a DiffuseLight (src/color.rs:8, zero for
             // every other material) or the albedo every scattering material but Dielectric multiplies in

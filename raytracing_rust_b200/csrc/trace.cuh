@@ -370,7 +370,7 @@ __device__ __forceinline__ void sphere_uv(V3f n, float* u, float* v) {  // src/s
 // when the material's texture chain can read them (ImageTexture); the reference computes
 // atan2/asin on every sphere hit (src/sphere.rs:50,64).
 __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim* __restrict__ prims, const RayF& ray,
-                                                const Hit& h) {
+                                                const Hit& h, int4* mat_record = nullptr) {
   Surface s;
   const float4 A = ldg4(&prims[h.prim].a);
   const float4 B = ldg4(&prims[h.prim].b);
@@ -379,7 +379,10 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
   const int xi = RTB_PRIM_XFORM(C.x);
   s.mat = C.y;
   s.u = 0.0f, s.v = 0.0f;
-  const bool need_uv = __ldg(&sv.mats[C.y].needs_uv) != 0;
+  // the material record (type, texture, parameter, needs_uv) in one load, handed on to the caller
+  const int4 mrec = __ldg(reinterpret_cast<const int4*>(sv.mats + C.y));
+  if (mat_record) *mat_record = mrec;
+  const bool need_uv = mrec.w != 0;
   if (type <= DP_MOVING_SPHERE) {
     V3f ctr = sphere_center(A, B, C, ray.time);
     s.p = madd(h.t, ray.d, ray.o);
@@ -563,7 +566,9 @@ __device__ __forceinline__ int sin10_negative(float x) { return ((int)floorf(x *
 template <bool kStats>
 __device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p, TexCounters* tc) {
   for (;;) {
+    // both halves of the 32-byte record at once: the colour load does not wait for the type test
     const int4 hd = __ldg(reinterpret_cast<const int4*>(sv.texs + tex));
+    const float4 col = __ldg(reinterpret_cast<const float4*>(sv.texs + tex) + 1);
     const int type = hd.x;
     if (kStats) tc->n[type & 3]++;
     if (type == RTB_TEX_CHECKER) {  // src/texture.rs:40-47: product of three sines < 0 -> `odd`
@@ -571,7 +576,6 @@ __device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float
       tex = neg ? hd.y : hd.z;
       continue;
     }
-    const float4 col = __ldg(reinterpret_cast<const float4*>(sv.texs + tex) + 1);
     if (type == RTB_TEX_SOLID) return mk(col.x, col.y, col.z);
     if (type == RTB_TEX_NOISE) {  // src/texture.rs:66-70
       float t = perlin_turb(sv.perlin + hd.y, p);
