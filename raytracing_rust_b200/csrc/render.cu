@@ -52,23 +52,6 @@ namespace rtb {
 // nothing else is runnable), so each phase's code executes with a well-filled warp instead of
 // the ~7/32 lanes a naive per-thread path loop reaches on these scenes (profiles/).
 // Radiance sums go to a per-warp shared-memory tile and to the accumulation buffer once.
-#ifndef RTB_STACK_TN
-#define RTB_STACK_TN 0  // measured slower: profiles/r1_experiments.txt
-#endif
-#if RTB_STACK_TN
-// Pops the traversal stack down to the first entry that can still hold a closer hit: a stacked (far) child whose box
-// is entered beyond the closest hit found since it was pushed is dropped without fetching or testing its node — the
-// same outcome node_step would reach for it (both grandchildren start at or beyond that distance), at 4 instructions
-// instead of a node fetch and two slab tests.
-__device__ __forceinline__ int pop_live(const int* stack, const float* stack_tn, int& sp, float t_best) {
-  while (sp > 0) {
-    --sp;
-    if (stack_tn[sp] <= t_best) return stack[sp];
-  }
-  return CUR_SHADE;
-}
-#endif
-
 // sample_media (trace.cuh) for media held in the kernel parameters: the same arithmetic as its sphere-boundary branch,
 // with the boundary, density and draw of each medium read from the constant bank instead of three dependent loads.
 template <bool kStats>
@@ -156,11 +139,10 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
     COLD_I(6) = 0;  // pix_local
   }
   int self_prim = -1, self_face = 0;
-  int stack[RTB_STACK_DEPTH];
-#if RTB_STACK_TN
-  float stack_tn[RTB_STACK_DEPTH];  // entry distance of each stacked child
-#endif
-  int sp = 0;
+  // traversal stack in local memory (L1): stack[0] holds CUR_SHADE for good, so a pop needs no emptiness test
+  int stack[RTB_STACK_DEPTH + 1];
+  stack[0] = CUR_SHADE;
+  int* top = stack + 1;
   int cur = CUR_WAIT;
   bool items_left = true;
   bool check_wait = true;  // warp-uniform
@@ -175,16 +157,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
       if (cur >= 0) {
         if (kStats) cnt.node_tests++;
         int next, push;
-#if RTB_STACK_TN
-        float push_tn;
-        const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push, &push_tn);
-        if (nh == 2) stack[sp] = push, stack_tn[sp] = push_tn, ++sp;
-        if (nh == 0) next = pop_live(stack, stack_tn, sp, best.t);
-#else
         const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-        if (nh == 2) stack[sp++] = push;
-        if (nh == 0) next = sp > 0 ? stack[--sp] : CUR_SHADE;
-#endif
+        if (nh == 2) *top++ = push;
+        if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
         cur = next;
       }
       m_node = __ballot_sync(0xffffffffu, cur >= 0);
@@ -332,7 +307,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           ri = make_ray_inv(ray);
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
-          sp = 0;
+          top = stack + 1;
           cur = sv.root;
         }
       }
@@ -341,16 +316,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
       if (cur >= 0) {  // below-threshold NODE step
         if (kStats) cnt.node_tests++;
         int next, push;
-#if RTB_STACK_TN
-        float push_tn;
-        const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push, &push_tn);
-        if (nh == 2) stack[sp] = push, stack_tn[sp] = push_tn, ++sp;
-        if (nh == 0) next = pop_live(stack, stack_tn, sp, best.t);
-#else
         const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-        if (nh == 2) stack[sp++] = push;
-        if (nh == 0) next = sp > 0 ? stack[--sp] : CUR_SHADE;
-#endif
+        if (nh == 2) *top++ = push;
+        if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
         cur = next;
       }
     } else {
@@ -368,11 +336,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             best.t = t, best.prim = pi, best.face = face, best.id = id;
           }
         }
-#if RTB_STACK_TN
-        cur = pop_live(stack, stack_tn, sp, best.t);
-#else
-        cur = sp > 0 ? stack[--sp] : CUR_SHADE;
-#endif
+        cur = *--top;
       }
     }
   }

@@ -275,7 +275,7 @@ __device__ __forceinline__ RayInv make_ray_inv(const RayF& ray) {
 // children hit (0, 1, 2); *next = the child to visit next (the nearer one), *push = the other
 // (valid when 2 is returned).
 __device__ __forceinline__ int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
-                                         int* next, int* push, float* push_tn = nullptr) {
+                                         int* next, int* push) {
   // two 256-bit loads (LDG.E.256.CONSTANT): (n0, n1) and (n2, n3)
   const Ld256 h0v = ld256(reinterpret_cast<const Ld256*>(nodes + cur));
   const Ld256 h1v = ld256(reinterpret_cast<const Ld256*>(nodes + cur) + 1);
@@ -298,7 +298,6 @@ __device__ __forceinline__ int node_step(const DNode* __restrict__ nodes, int cu
   if (h0 && h1) {
     *next = swap ? c1 : c0;
     *push = swap ? c0 : c1;
-    if (push_tn) *push_tn = fmaxf(tn0, tn1);  // entry distance of the far child: pops cull on it once a nearer hit exists
     return 2;
   }
   *next = h0 ? c0 : c1;
