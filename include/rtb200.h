@@ -242,6 +242,27 @@ int rtb_primary_rays(const RtbCamera*, int nx, int ny, int s, uint64_t seed, dou
 int rtb_debug_texture_value(rtb_scene*, int world, int tex, const double* uvp, size_t n, int device,
                             float* out);
 
+/* ---- field-level parity hooks (csrc/debug.cu): one stage of the device path at a time ------------------------
+ * rtb_closest_hit_ex: rtb_closest_hit plus (a) self_id (optional, n entries): the primitive ID of the surface ray i
+ * leaves (-1: none).  The kernels exclude that surface's own root analytically where the f64 reference relies on
+ * t_min = 0.001 (src/color.rs:7); this is the query every scattered ray of a render issues.  (b) out_rec (optional):
+ * n x {t, u, v, p.xyz, normal.xyz} = the HitRecord of src/hittable.rs:9-16 (u,v always computed, as upstream). */
+int rtb_closest_hit_ex(rtb_scene*, int world, const double* rays, size_t n, double t_min, const int32_t* self_id,
+                       int device, int32_t* out_prim, float* out_rec);
+/* Camera::get_ray (src/camera.rs:53-67) evaluated by the device code of the render kernels (f32) for sample `s` of
+ * every pixel: out = nx*ny x {o.xyz, d.xyz, time} floats.  rtb_primary_rays is the same batch in host f64. */
+int rtb_debug_camera_rays(const RtbCamera*, int nx, int ny, int s, uint64_t seed, int device, float* out_rays);
+/* The random inputs behind that batch, in the layout an explicit-input get_ray wants: nx*ny x {s, t, rd.x, rd.y,
+ * xi_time} with rd the unit-disk point of src/util.rs:15-24 (before the lens-radius scale).  Host code. */
+int rtb_debug_camera_draws(int nx, int ny, int s, uint64_t seed, double* out);
+/* Material::scatter (src/material.rs:49-168) + the albedo lookup as the SHADE phase runs them.  in = n x {ray o.xyz,
+ * d.xyz, time, hit t, u, v, p.xyz, normal.xyz} (16 doubles); out = n x {scattered?, o.xyz, d.xyz, attenuation.rgb}
+ * (10 floats, zeros when the path ends).  Item i uses the bounce-0 draws of (pixel i, sample 0) under `seed`. */
+int rtb_debug_scatter(rtb_scene*, int world, int mat, const double* in, size_t n, uint64_t seed, int device, float* out);
+/* The device samplers that replace the rejection loops of src/util.rs:4-24: kind 0 = uniform in the unit ball (scatter),
+ * kind 1 = uniform in the unit disk (lens).  out = n x {x, y, z} floats. */
+int rtb_debug_sample(int kind, uint64_t seed, size_t n, int device, float* out);
+
 /* P3 text exactly as tests/test.rs:59,79: "P3\n{nx} {ny}\n255\n" + "{r} {g} {b}\n" per pixel.
  * Returns the byte count (excluding NUL); writes at most cap bytes. */
 size_t rtb_ppm_p3(const uint8_t* rgb8, int nx, int ny, char* out, size_t cap);

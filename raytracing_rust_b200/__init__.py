@@ -136,6 +136,11 @@ _sig("rtb_peer_close", _i, _vp)
 _sig("rtb_reduce_resolve_device", _i, C.POINTER(C.c_void_p), _i, _i, _i, _i, _vp, _vp, _vp)
 _sig("rtb_closest_hit", _i, _vp, _i, _vp, _sz, _d, _i, _vp, _vp)
 _sig("rtb_debug_texture_value", _i, _vp, _i, _i, _vp, _sz, _i, _vp)
+_sig("rtb_closest_hit_ex", _i, _vp, _i, _vp, _sz, _d, _vp, _i, _vp, _vp)
+_sig("rtb_debug_camera_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _i, _vp)
+_sig("rtb_debug_camera_draws", _i, _i, _i, _i, _u64, _vp)
+_sig("rtb_debug_scatter", _i, _vp, _i, _i, _vp, _sz, _u64, _i, _vp)
+_sig("rtb_debug_sample", _i, _i, _u64, _sz, _i, _vp)
 _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
 _sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
 _sig("rtb_ppm_p6", _sz, _vp, _i, _i, _vp, _sz)
@@ -409,6 +414,25 @@ class Scene:
            "closest_hit")
         return prim, t
 
+    def closest_hit_ex(self, world, rays: np.ndarray, self_id=None, t_min=1e-3, device=0, want_rec=True):
+        """rtb_closest_hit_ex: rays [n,7] float64; self_id [n] int32 primitive ID each ray leaves (-1 none) or None.
+        Returns (prim int32 [n], rec float32 [n,9] {t,u,v,p,normal} or None)."""
+        r = np.ascontiguousarray(rays, dtype=np.float64)
+        n = r.shape[0]
+        sid = None if self_id is None else np.ascontiguousarray(self_id, dtype=np.int32)
+        prim = np.empty(n, np.int32)
+        rec = np.empty((n, 9), np.float32) if want_rec else None
+        _h(lib.rtb_closest_hit_ex(self._p, world, r.ctypes.data, n, t_min, sid.ctypes.data if sid is not None else None,
+                                  device, prim.ctypes.data, rec.ctypes.data if want_rec else None), "closest_hit_ex")
+        return prim, rec
+
+    def scatter(self, world, mat, inp: np.ndarray, seed=1, device=0):
+        """rtb_debug_scatter: inp [n,16] {ray o,d,time, hit t,u,v,p,normal}; returns [n,10] {ok, o, d, atten}."""
+        q = np.ascontiguousarray(inp, dtype=np.float64)
+        out = np.empty((q.shape[0], 10), np.float32)
+        _h(lib.rtb_debug_scatter(self._p, world, mat, q.ctypes.data, q.shape[0], seed, device, out.ctypes.data), "debug_scatter")
+        return out
+
     def texture_value(self, world, tex, uvp: np.ndarray, device=0):
         q = np.ascontiguousarray(uvp, dtype=np.float64)
         out = np.empty((q.shape[0], 3), np.float32)
@@ -480,6 +504,27 @@ def reduce_resolve_device(sum_ptrs, nx, ny, ns, d_rgb8_ptr: int, d_total_ptr: in
 def primary_rays(cam, nx, ny, sample=0, seed=1) -> np.ndarray:
     out = np.empty((nx * ny, 7), np.float64)
     _h(lib.rtb_primary_rays(C.byref(cam), nx, ny, sample, seed, out.ctypes.data), "primary_rays")
+    return out
+
+
+def device_camera_rays(cam, nx, ny, sample=0, seed=1, device=0) -> np.ndarray:
+    """Camera::get_ray as the render kernels evaluate it (device f32): [nx*ny, 7] float32."""
+    out = np.empty((nx * ny, 7), np.float32)
+    _h(lib.rtb_debug_camera_rays(C.byref(cam), nx, ny, sample, seed, device, out.ctypes.data), "debug_camera_rays")
+    return out
+
+
+def camera_draws(nx, ny, sample=0, seed=1) -> np.ndarray:
+    """The draws behind primary_rays / device_camera_rays as explicit get_ray inputs: [nx*ny, 5] {s,t,rd.x,rd.y,xi_time}."""
+    out = np.empty((nx * ny, 5), np.float64)
+    _h(lib.rtb_debug_camera_draws(nx, ny, sample, seed, out.ctypes.data), "debug_camera_draws")
+    return out
+
+
+def device_sample(kind, seed, n, device=0) -> np.ndarray:
+    """Device samplers (0 = unit ball, 1 = unit disk): [n, 3] float32."""
+    out = np.empty((n, 3), np.float32)
+    _h(lib.rtb_debug_sample(kind, seed, n, device, out.ctypes.data), "debug_sample")
     return out
 
 

@@ -6,7 +6,8 @@
 // a single process, so this entry point does the same thing inside it:
 //   * one host thread per device renders the sample slice  s = i, i + G, i + 2G, ...  of every
 //     pixel into that device's accumulation buffer (counter-based draws: the union of the slices
-//     is exactly the single-GPU sample set, so the image does not depend on G),
+//     is exactly the single-GPU sample set: same samples whatever G is, sums equal up to float addition order,
+//     i.e. <= 1 LSB after quantisation),
 //   * the first device then runs the fused reduce + resolve kernel of peer.cu over all G buffers
 //     through peer access (NVLink loads; buffers of devices without peer access are staged with
 //     cudaMemcpyPeer first), and the image goes to the host once.
@@ -83,6 +84,9 @@ extern "C" int rtb_render_multi(rtb_scene* s, int world, const RtbCamera* camera
       if (devs[j] == devs[i]) return fail(RTB_ERR_INVALID, "render_multi: device listed twice");
   }
   const int G = (int)std::min<size_t>(devs.size(), (size_t)ns);  // never more shards than samples
+  // "the current world" (world < 0) is a property of the caller's handle: resolve it once, the replicas have none
+  if (world < 0) world = s->dev_world;
+  if (!s->obj_ok(world)) return fail(RTB_ERR_INVALID, "render_multi: bad world handle");
 
   // replicas of the scene for devices 1..G-1 (a scene handle holds one device copy), rebuilt when the scene changed
   if (G > 1) {
@@ -94,7 +98,12 @@ extern "C" int rtb_render_multi(rtb_scene* s, int world, const RtbCamera* camera
       s->replicas.clear();
       for (int i = 1; i < G; ++i) {
         rtb_scene* r = rtb_scene_deserialize(blob.data(), blob.size());
-        if (!r) return RTB_ERR_INVALID;
+        if (!r) {  // leave no half-built replica set behind a stale blob
+          for (rtb_scene* q : s->replicas) delete q;
+          s->replicas.clear();
+          s->replica_blob.clear();
+          return RTB_ERR_INVALID;
+        }
         r->bvh_builder = s->bvh_builder;
         s->replicas.push_back(r);
       }

@@ -5,11 +5,9 @@
 //   color         src/color.rs:6-23     (emitted + attenuation * color(scattered), depth < 50)
 //
 // Kernels in this file
-//   k_render_mega   persistent per-thread path loop with regeneration: a thread owns one pixel
-//                   (or one sample slice of it), runs one ray segment per loop iteration and
-//                   starts its next camera sample as soon as a path ends, so a warp only idles
-//                   in the tail of its sample budget.  Radiance sums stay in registers and are
-//                   added to the accumulation buffer once per launch.
+//   k_render_mega   persistent warps that draw (8x4 pixel tile x sample slice) work items and advance their 32 paths
+//                   with a NODE / LEAF / SHADE scheduler chosen by ballot (see the comment at the kernel); radiance
+//                   goes to per-warp shared-memory tiles and to the accumulation buffer once per item.
 //   k_closest_hit   primary-ray closest-hit query for the primitive-ID parity test.
 //   k_resolve       /ns, sqrt, clamp, 255.99 truncation (tests/test.rs:71-78).
 //   k_texture_eval  Texture::value over a batch (parity tests).
@@ -23,6 +21,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -73,7 +72,7 @@ __device__ __forceinline__ int sample_media_const(const MegaParams& P, const Ray
     const float disc = fmaf(S.w, S.w, -dot(l, l));
     const float h = sqrt_fast(fmaxf(disc, 0.0f) * inv_a);
     float t1 = tc - h, t2 = tc + h;
-    if (!(disc > 0.0f && t2 > t1 + 0.0001f)) continue;
+    if (!(disc > 0.0f && t2 > medium_restart(t1))) continue;
     if (t1 < P.t_min) t1 = P.t_min;
     if (t2 > *t_closest) t2 = *t_closest;
     if (t1 < t2) {
@@ -463,16 +462,15 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
     s->dev = nullptr;
   }
   StageTimer tm("upload");
-  DeviceScene* d = new DeviceScene();
+  // owned until the very end: every early return (CUDA_TRY included) releases the device allocations made so far
+  std::unique_ptr<DeviceScene, void (*)(DeviceScene*)> owner(new DeviceScene(), destroy_device_scene);
+  DeviceScene* d = owner.get();
   d->device = device;
   // who builds the BVH: the host's full-sweep SAH (best trees; O(n log^2 n)) or the device LBVH (bvh_build.cu)
   int builder = s->bvh_builder;
   if (builder == RTB_BVH_AUTO) builder = rtb_scene_prim_count(s, world) >= RTB_BVH_AUTO_DEVICE_MIN ? RTB_BVH_DEVICE_LBVH : RTB_BVH_HOST_SAH;
   int rc = flatten_scene(*s, world, tlo, thi, &d->flat, builder != RTB_BVH_DEVICE_LBVH);
-  if (rc != RTB_OK) {
-    delete d;
-    return rc;
-  }
+  if (rc != RTB_OK) return rc;
   tm.lap("flatten + host BVH");
   CUDA_TRY(cudaSetDevice(device));
   tm.lap("cudaSetDevice");
@@ -480,19 +478,14 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   const FlatScene& f = d->flat;
   const bool device_bvh = f.root < 0;  // flatten left the tree to the device builder
   if (device_bvh) {
-    if ((rc = build_bvh_device(d)) != RTB_OK) {
-      destroy_device_scene(d);
-      return rc;
-    }
+    if ((rc = build_bvh_device(d)) != RTB_OK) return rc;
   } else if ((rc = upload_vec(d, f.nodes, &v.nodes)) || (rc = upload_vec(d, f.prims, &v.prims))) {
-    destroy_device_scene(d);
     return rc;
   }
   if ((rc = upload_vec(d, f.bprims, &v.bprims)) || (rc = upload_vec(d, f.media, &v.media)) ||
       (rc = upload_vec(d, f.xforms, &v.xforms)) || (rc = upload_vec(d, f.mats, &v.mats)) ||
       (rc = upload_vec(d, f.texs, &v.texs)) || (rc = upload_vec(d, f.perlin, &v.perlin)) ||
       (rc = upload_vec(d, f.texels, &v.texels))) {
-    destroy_device_scene(d);
     return rc;
   }
   tm.lap("table uploads");
@@ -511,7 +504,7 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   // only the SM count is used; cudaGetDeviceProperties costs 2-4 ms per call
   CUDA_TRY(cudaDeviceGetAttribute(&d->prop.multiProcessorCount, cudaDevAttrMultiProcessorCount, device));
   tm.lap("device attributes");
-  s->dev = d;
+  s->dev = owner.release();
   s->dev_world = world;
   if (std::getenv("RTB200_DEBUG"))
     std::fprintf(stderr, "[rtb200] uploaded: %d nodes (%s), %zu prims, %zu boundary prims, %zu media, %zu xforms, bvh depth %d\n",
@@ -678,7 +671,14 @@ int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int
   DCamera cam;
   make_device_camera(*camera, &cam);
   uint64_t launches = 0;
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  struct Events {  // destroyed on every return path
+    cudaEvent_t a = nullptr, b = nullptr;
+    ~Events() {
+      if (a) cudaEventDestroy(a);
+      if (b) cudaEventDestroy(b);
+    }
+  } evs;
+  cudaEvent_t &e0 = evs.a, &e1 = evs.b;
   if (stats) {
     CUDA_TRY(cudaMemsetAsync(d->d_stats, 0, 32 * sizeof(unsigned long long), stream));
     CUDA_TRY(cudaEventCreate(&e0));
@@ -702,8 +702,6 @@ int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int
     CUDA_TRY(cudaEventSynchronize(e1));
     float ms = 0;
     CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
     unsigned long long h[32];
     CUDA_TRY(cudaMemcpy(h, d->d_stats, sizeof h, cudaMemcpyDeviceToHost));
     std::memset(stats, 0, sizeof *stats);
@@ -795,9 +793,11 @@ struct OutputStager {
   void start(int device, void* p, size_t bytes) {
     ptr = p;
     th = std::thread([this, device, p, bytes]() {
+      // fault the pages in WITHOUT changing them: a failed render must leave the caller's buffer as it was.  (A never-touched
+      // anonymous page reads through the shared zero page, so a read alone would not allocate it: write back what was read.)
       volatile uint8_t* b = (volatile uint8_t*)p;
-      for (size_t i = 0; i < bytes; i += 4096) b[i] = 0;
-      if (bytes) b[bytes - 1] = 0;
+      for (size_t i = 0; i < bytes; i += 4096) b[i] = b[i];
+      if (bytes) b[bytes - 1] = b[bytes - 1];
       if (cudaSetDevice(device) == cudaSuccess && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned = true;
       else cudaGetLastError();
     });
@@ -904,8 +904,11 @@ int rtb_render_progressive(rtb_scene* s, int world, const RtbCamera* camera, int
     return code;
   };
   if (cudaMemset(d_sum, 0, n * sizeof(float)) != cudaSuccess) return finish(fail(RTB_ERR_CUDA, "memset"));
-  cudaEvent_t e0, e1;
-  cudaEventCreate(&e0), cudaEventCreate(&e1);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (cudaEventCreate(&e0) != cudaSuccess || cudaEventCreate(&e1) != cudaSuccess) {
+    if (e0) cudaEventDestroy(e0);
+    return finish(fail(RTB_ERR_CUDA, "render_progressive: cudaEventCreate failed"));
+  }
   int done = 0, chunks = 0;
   double gpu_s = 0.0;
   bool stop = false;

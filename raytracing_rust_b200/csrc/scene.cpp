@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <exception>
 #include <vector>
 
 namespace rtb {
@@ -316,21 +317,33 @@ rtb_scene* rtb_scene_deserialize(const void* buf, size_t len) {
     rtb::set_error("deserialize: bad magic/version");
     return nullptr;
   }
-  size_t need = sizeof h + (size_t)h.n_tex * sizeof(RtbTexRec) + (size_t)h.n_mat * sizeof(RtbMatRec) +
-                (size_t)h.n_obj * sizeof(RtbObjRec) + (size_t)h.n_list * sizeof(int32_t) +
-                (size_t)h.n_perlin * sizeof(RtbPerlinTable) + (size_t)h.n_image_bytes;
-  if (len < need) {
+  // every count is bounded by the bytes that are left before it is multiplied or added: a header cannot make the sum wrap
+  size_t left = len - sizeof h;
+  auto take = [&left](uint64_t count, size_t each) {
+    if (count > left / each) return false;
+    left -= (size_t)count * each;
+    return true;
+  };
+  if (!take(h.n_tex, sizeof(RtbTexRec)) || !take(h.n_mat, sizeof(RtbMatRec)) || !take(h.n_obj, sizeof(RtbObjRec)) ||
+      !take(h.n_list, sizeof(int32_t)) || !take(h.n_perlin, sizeof(RtbPerlinTable)) || !take(h.n_image_bytes, 1)) {
     rtb::set_error("deserialize: truncated");
     return nullptr;
   }
-  rtb_scene* s = new rtb_scene();
+  rtb_scene* s = nullptr;
+  try {
+    s = new rtb_scene();
+    s->tex.resize(h.n_tex), s->mat.resize(h.n_mat), s->obj.resize(h.n_obj);
+    s->list_pool.resize(h.n_list), s->perlin.resize(h.n_perlin), s->image_pool.resize((size_t)h.n_image_bytes);
+  } catch (const std::exception&) {  // nothing may unwind through the extern "C" boundary
+    delete s;
+    rtb::set_error("deserialize: out of memory");
+    return nullptr;
+  }
   const uint8_t* p = (const uint8_t*)buf + sizeof h;
   auto get = [&p](void* dst, size_t n) {
     if (n) std::memcpy(dst, p, n);
     p += n;
   };
-  s->tex.resize(h.n_tex), s->mat.resize(h.n_mat), s->obj.resize(h.n_obj);
-  s->list_pool.resize(h.n_list), s->perlin.resize(h.n_perlin), s->image_pool.resize(h.n_image_bytes);
   get(s->tex.data(), s->tex.size() * sizeof(RtbTexRec));
   get(s->mat.data(), s->mat.size() * sizeof(RtbMatRec));
   get(s->obj.data(), s->obj.size() * sizeof(RtbObjRec));
@@ -339,21 +352,42 @@ rtb_scene* rtb_scene_deserialize(const void* buf, size_t len) {
   get(s->image_pool.data(), s->image_pool.size());
   // validate handles so later walks cannot index out of range
   bool ok = true;
-  for (auto& t : s->tex) {
-    if (t.type == RTB_TEX_CHECKER) ok &= s->tex_ok(t.a) && s->tex_ok(t.b);
-    if (t.type == RTB_TEX_NOISE) ok &= t.a >= 0 && (size_t)t.a < s->perlin.size();
-    if (t.type == RTB_TEX_IMAGE)
-      ok &= t.a > 0 && t.b > 0 && t.image_off + (uint64_t)t.a * t.b * 3 <= s->image_pool.size();
+  for (size_t i = 0; i < s->tex.size(); ++i) {
+    const auto& t = s->tex[i];
+    switch (t.type) {
+      case RTB_TEX_SOLID: break;
+      case RTB_TEX_CHECKER:  // children precede parents, as the builders create them: no cycles (a self-referencing checker
+        // would recurse without end in flatten's tex_needs_uv and spin in the device's texture_value loop)
+        ok &= t.a >= 0 && (size_t)t.a < i && t.b >= 0 && (size_t)t.b < i;
+        break;
+      case RTB_TEX_NOISE: ok &= t.a >= 0 && (size_t)t.a < s->perlin.size(); break;
+      case RTB_TEX_IMAGE: {
+        const uint64_t pool = s->image_pool.size();
+        ok &= t.a > 0 && t.b > 0 && t.image_off <= pool && (uint64_t)t.a * (uint64_t)t.b <= (pool - std::min<uint64_t>(t.image_off, pool)) / 3;
+        break;
+      }
+      default: ok = false;  // an unknown type would fall through to the image branch on the device
+    }
   }
-  for (auto& m : s->mat)
+  for (auto& m : s->mat) {
+    ok &= m.type >= RTB_MAT_LAMBERTIAN && m.type <= RTB_MAT_ISOTROPIC;
     if (m.type != RTB_MAT_DIELECTRIC) ok &= s->tex_ok(m.tex);
+  }
   for (size_t i = 0; i < s->obj.size(); ++i) {
     auto& o = s->obj[i];
     switch (o.type) {
-      case RTB_OBJ_SPHERE: case RTB_OBJ_MOVING_SPHERE: case RTB_OBJ_RECT: case RTB_OBJ_CUBE:
+      case RTB_OBJ_RECT:
+        ok &= o.sel >= RTB_PLANE_YZ && o.sel <= RTB_PLANE_XY;
         ok &= s->mat_ok(o.mat);
         break;
-      case RTB_OBJ_FLIP_NORMALS: case RTB_OBJ_ROTATE: case RTB_OBJ_TRANSLATE:
+      case RTB_OBJ_SPHERE: case RTB_OBJ_MOVING_SPHERE: case RTB_OBJ_CUBE:
+        ok &= s->mat_ok(o.mat);
+        break;
+      case RTB_OBJ_ROTATE:
+        ok &= o.sel >= RTB_AXIS_X && o.sel <= RTB_AXIS_Z;
+        ok &= o.child >= 0 && (size_t)o.child < i;
+        break;
+      case RTB_OBJ_FLIP_NORMALS: case RTB_OBJ_TRANSLATE:
         ok &= o.child >= 0 && (size_t)o.child < i;  // children precede parents: no cycles
         break;
       case RTB_OBJ_CONSTANT_MEDIUM:

@@ -3,8 +3,15 @@
 // material scattering.  f32 throughout; each routine cites the f64 reference code whose result
 // it reproduces.
 #pragma once
+#if defined(RTB_HOST_EMUL)
+// developer build only (tools/host_emul): the same source compiled for the host by g++, to debug kernel LOGIC in a
+// container without a GPU.  Never part of librtb200.so.
+#include "host_emul_shim.h"
+#else
 #include <cuda_runtime.h>
 #include <math_constants.h>
+#define RTB_DEV __device__ __forceinline__
+#endif
 
 #include "device_types.h"
 #include "philox.h"
@@ -16,60 +23,76 @@ namespace rtb {
 struct V3f {
   float x, y, z;
 };
-__device__ __forceinline__ V3f mk(float x, float y, float z) { return V3f{x, y, z}; }
-__device__ __forceinline__ V3f operator+(V3f a, V3f b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
-__device__ __forceinline__ V3f operator-(V3f a, V3f b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
-__device__ __forceinline__ V3f operator-(V3f a) { return mk(-a.x, -a.y, -a.z); }
-__device__ __forceinline__ V3f operator*(float s, V3f a) { return mk(s * a.x, s * a.y, s * a.z); }
-__device__ __forceinline__ V3f operator*(V3f a, V3f b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
-__device__ __forceinline__ float dot(V3f a, V3f b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
-__device__ __forceinline__ V3f madd(float t, V3f d, V3f o) {  // o + t*d
+RTB_DEV V3f mk(float x, float y, float z) { return V3f{x, y, z}; }
+RTB_DEV V3f operator+(V3f a, V3f b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+RTB_DEV V3f operator-(V3f a, V3f b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+RTB_DEV V3f operator-(V3f a) { return mk(-a.x, -a.y, -a.z); }
+RTB_DEV V3f operator*(float s, V3f a) { return mk(s * a.x, s * a.y, s * a.z); }
+RTB_DEV V3f operator*(V3f a, V3f b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+RTB_DEV float dot(V3f a, V3f b) { return fmaf(a.x, b.x, fmaf(a.y, b.y, a.z * b.z)); }
+RTB_DEV V3f madd(float t, V3f d, V3f o) {  // o + t*d
   return mk(fmaf(t, d.x, o.x), fmaf(t, d.y, o.y), fmaf(t, d.z, o.z));
 }
-__device__ __forceinline__ float comp(V3f v, int axis) { return axis == 0 ? v.x : (axis == 1 ? v.y : v.z); }
-__device__ __forceinline__ void set_comp(V3f& v, int axis, float s) {
+RTB_DEV float comp(V3f v, int axis) { return axis == 0 ? v.x : (axis == 1 ? v.y : v.z); }
+RTB_DEV void set_comp(V3f& v, int axis, float s) {
   if (axis == 0) v.x = s;
   else if (axis == 1) v.y = s;
   else v.z = s;
 }
 
-__device__ __forceinline__ float4 ldg4(const f4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
-__device__ __forceinline__ int4 ldg4i(const i4* p) { return __ldg(reinterpret_cast<const int4*>(p)); }
+RTB_DEV float4 ldg4(const f4* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+RTB_DEV int4 ldg4i(const i4* p) { return __ldg(reinterpret_cast<const int4*>(p)); }
 // one 256-bit read-only load (sm_100a: ld.global.nc.v8.f32 -> LDG.E.256.CONSTANT); p is 32-byte aligned
 struct alignas(32) Ld256 {
   float v[8];
 };
-__device__ __forceinline__ Ld256 ld256(const Ld256* p) {
+RTB_DEV Ld256 ld256(const Ld256* p) {
   Ld256 r;
+#if defined(RTB_HOST_EMUL)
+  return *p;
+#else
   asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
       : "=f"(r.v[0]), "=f"(r.v[1]), "=f"(r.v[2]), "=f"(r.v[3]), "=f"(r.v[4]), "=f"(r.v[5]), "=f"(r.v[6]), "=f"(r.v[7])
       : "l"(p));
   return r;
+#endif
 }
 
 // Single-instruction SFU forms (MUFU.RCP / RSQ / SQRT / EX2 / LG2, <= 2 ulp).  The f64 reference
 // is matched statistically and through closest-hit IDs, not bit-wise, so the IEEE-rounded
 // division / sqrt sequences (and their slow-path subroutines) buy nothing here.
-__device__ __forceinline__ float rcp_fast(float x) {
+RTB_DEV float rcp_fast(float x) {
+#if defined(RTB_HOST_EMUL)
+  return 1.0f / x;
+#else
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
+#endif
 }
-__device__ __forceinline__ float sqrt_fast(float x) {
+RTB_DEV float sqrt_fast(float x) {
+#if defined(RTB_HOST_EMUL)
+  return sqrtf(x);
+#else
   float r;
   asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
+#endif
 }
-__device__ __forceinline__ float rsqrt_fast(float x) {
+RTB_DEV float rsqrt_fast(float x) {
+#if defined(RTB_HOST_EMUL)
+  return 1.0f / sqrtf(x);
+#else
   float r;
   asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;
+#endif
 }
-__device__ __forceinline__ float cbrt_fast01(float x) {  // x in (0,1): 2^(log2(x)/3)
+RTB_DEV float cbrt_fast01(float x) {  // x in (0,1): 2^(log2(x)/3)
   return exp2f(__log2f(x) * (1.0f / 3.0f));
 }
 // sin(x) for |x| up to ~1e5: two-constant Cody-Waite reduction to [-pi, pi], then MUFU.SIN
-__device__ __forceinline__ float sin_reduced(float x) {
+RTB_DEV float sin_reduced(float x) {
   float k = rintf(x * 0.15915494309189535f);
   float r = fmaf(-k, 6.2831854820251465f, x);  // 2*pi rounded to f32
   r = fmaf(-k, -1.7484555e-7f, r);              // 2*pi - fl(2*pi)
@@ -86,7 +109,7 @@ __device__ __forceinline__ float sin_reduced(float x) {
 
 // uniform in the unit ball == the distribution of the rejection loop at src/util.rs:4-13,
 // sampled directly from 3 draws (no divergence)
-__device__ __forceinline__ V3f sample_unit_ball(float r0, float r1, float r2) {
+RTB_DEV V3f sample_unit_ball(float r0, float r1, float r2) {
   float z = 1.0f - 2.0f * r0;
   float phi = (2.0f * r1 - 1.0f) * CUDART_PI_F;
   float r = cbrt_fast01(r2);
@@ -109,24 +132,24 @@ struct Hit {
   int id;    // primitive ID of the hit (first ID + face), for the tie rule
 };
 
-__device__ __forceinline__ V3f xf_point(const DXform& x, V3f p) {  // local = M p + b
+RTB_DEV V3f xf_point(const DXform& x, V3f p) {  // local = M p + b
   return mk(fmaf(x.m[0], p.x, fmaf(x.m[1], p.y, fmaf(x.m[2], p.z, x.b[0]))),
             fmaf(x.m[3], p.x, fmaf(x.m[4], p.y, fmaf(x.m[5], p.z, x.b[1]))),
             fmaf(x.m[6], p.x, fmaf(x.m[7], p.y, fmaf(x.m[8], p.z, x.b[2]))));
 }
-__device__ __forceinline__ V3f xf_vec(const DXform& x, V3f v) {  // M v
+RTB_DEV V3f xf_vec(const DXform& x, V3f v) {  // M v
   return mk(fmaf(x.m[0], v.x, fmaf(x.m[1], v.y, x.m[2] * v.z)), fmaf(x.m[3], v.x, fmaf(x.m[4], v.y, x.m[5] * v.z)),
             fmaf(x.m[6], v.x, fmaf(x.m[7], v.y, x.m[8] * v.z)));
 }
-__device__ __forceinline__ V3f xf_vec_t(const DXform& x, V3f v) {  // M^T v
+RTB_DEV V3f xf_vec_t(const DXform& x, V3f v) {  // M^T v
   return mk(fmaf(x.m[0], v.x, fmaf(x.m[3], v.y, x.m[6] * v.z)), fmaf(x.m[1], v.x, fmaf(x.m[4], v.y, x.m[7] * v.z)),
             fmaf(x.m[2], v.x, fmaf(x.m[5], v.y, x.m[8] * v.z)));
 }
-__device__ __forceinline__ V3f xf_point_inv(const DXform& x, V3f p) {  // world = M^T (p - b)
+RTB_DEV V3f xf_point_inv(const DXform& x, V3f p) {  // world = M^T (p - b)
   return xf_vec_t(x, mk(p.x - x.b[0], p.y - x.b[1], p.z - x.b[2]));
 }
 
-__device__ __forceinline__ DXform load_xform(const DXform* xs, int i) {
+RTB_DEV DXform load_xform(const DXform* xs, int i) {
   DXform x;
   const float4* p = reinterpret_cast<const float4*>(xs + i);
   float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
@@ -137,7 +160,7 @@ __device__ __forceinline__ DXform load_xform(const DXform* xs, int i) {
   return x;
 }
 
-__device__ __forceinline__ V3f sphere_center(float4 a, float4 b, int4 c, float time) {
+RTB_DEV V3f sphere_center(float4 a, float4 b, int4 c, float time) {
   // MovingSphere::center, src/sphere.rs:115-118
   V3f ctr = mk(a.x, a.y, a.z);
   if (RTB_PRIM_TYPE(c.x) == DP_MOVING_SPHERE) {
@@ -163,7 +186,7 @@ struct Counters {
 // Plane distances are always (k - o) * rcp(d), in Rect and Box alike, so coincident planes
 // (a cube standing on a floor rect) produce bit-identical t and the ID tie rule can apply.
 template <bool kStats>
-__device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXform* __restrict__ xforms,
+RTB_DEV bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXform* __restrict__ xforms,
                                                const RayF& ray, float inv_a, float t_min, float t_max, bool self,
                                                int self_face, float* t_out, int* face_out, int* id_out, Counters* cnt) {
   if (kStats) cnt->prim_tests++;
@@ -263,7 +286,7 @@ __device__ __forceinline__ bool intersect_prim(const DPrim* __restrict__ prims, 
 struct RayInv {  // per-ray constants of the slab test
   float idx, idy, idz, oodx, oody, oodz;
 };
-__device__ __forceinline__ RayInv make_ray_inv(const RayF& ray) {
+RTB_DEV RayInv make_ray_inv(const RayF& ray) {
   auto safe_inv = [](float v) { return rcp_fast(fabsf(v) > 1e-20f ? v : copysignf(1e-20f, v)); };
   RayInv r;
   r.idx = safe_inv(ray.d.x), r.idy = safe_inv(ray.d.y), r.idz = safe_inv(ray.d.z);
@@ -274,7 +297,7 @@ __device__ __forceinline__ RayInv make_ray_inv(const RayF& ray) {
 // Tests both children of inner node `cur` against (t_min, t_best).  Returns the number of
 // children hit (0, 1, 2); *next = the child to visit next (the nearer one), *push = the other
 // (valid when 2 is returned).
-__device__ __forceinline__ int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
+RTB_DEV int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
                                          int* next, int* push) {
   // two 256-bit loads (LDG.E.256.CONSTANT): (n0, n1) and (n2, n3)
   const Ld256 h0v = ld256(reinterpret_cast<const Ld256*>(nodes + cur));
@@ -313,7 +336,7 @@ __device__ __forceinline__ int node_step(const DNode* __restrict__ nodes, int cu
 // planar primitive replaces an earlier one at equal t (Q23; e.g. cornell_box's two floors and
 // the cube bottoms resting on them); later == higher primitive ID, which is what wins here.
 template <bool kStats>
-__device__ __forceinline__ Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int self_prim,
+RTB_DEV Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int self_prim,
                                              int self_face, Counters* cnt) {
   Hit best;
   best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
@@ -358,7 +381,7 @@ struct Surface {
   int mat;
 };
 
-__device__ __forceinline__ void sphere_uv(V3f n, float* u, float* v) {  // src/sphere.rs:9-15 (Q5: FRAC_2_PI)
+RTB_DEV void sphere_uv(V3f n, float* u, float* v) {  // src/sphere.rs:9-15 (Q5: FRAC_2_PI)
   float phi = atan2f(n.z, n.x);
   float theta = asinf(fminf(1.0f, fmaxf(-1.0f, n.y)));
   *u = 1.0f - (phi + CUDART_PI_F) * (0.5f / CUDART_PI_F);
@@ -368,8 +391,8 @@ __device__ __forceinline__ void sphere_uv(V3f n, float* u, float* v) {  // src/s
 // Fills the HitRecord fields (src/hittable.rs:9-16) of an accepted hit.  u,v are only computed
 // when the material's texture chain can read them (ImageTexture); the reference computes
 // atan2/asin on every sphere hit (src/sphere.rs:50,64).
-__device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim* __restrict__ prims, const RayF& ray,
-                                                const Hit& h, int4* mat_record = nullptr) {
+RTB_DEV Surface finalize_hit(const SceneView& sv, const DPrim* __restrict__ prims, const RayF& ray,
+                                                const Hit& h, int4* mat_record = nullptr, bool force_uv = false) {
   Surface s;
   const float4 A = ldg4(&prims[h.prim].a);
   const float4 B = ldg4(&prims[h.prim].b);
@@ -381,7 +404,7 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
   // the material record (type, texture, parameter, needs_uv) in one load, handed on to the caller
   const int4 mrec = __ldg(reinterpret_cast<const int4*>(sv.mats + C.y));
   if (mat_record) *mat_record = mrec;
-  const bool need_uv = mrec.w != 0;
+  const bool need_uv = force_uv || mrec.w != 0;  // force_uv: the field-level parity hook (debug.cu) wants every record complete
   if (type <= DP_MOVING_SPHERE) {
     V3f ctr = sphere_center(A, B, C, ray.time);
     s.p = madd(h.t, ray.d, ray.o);
@@ -435,6 +458,33 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
   return s;
 }
 
+// Slab interval [t_enter, t_exit] of the ray's LINE against a BOX primitive (the six Rects of src/cube.rs:21-74 over
+// (-MAX, MAX)): the two boundary hits ConstantMedium::hit asks for (src/medium.rs:30-31) in one pass.
+RTB_DEV bool box_interval(const DPrim* __restrict__ prims, int pi, const int4 C, const DXform* __restrict__ xforms, const RayF& ray,
+                          float* t_enter, float* t_exit) {
+  const float4 A = ldg4(&prims[pi].a);
+  const float4 B = ldg4(&prims[pi].b);
+  V3f o = ray.o, d = ray.d;
+  const int xi = RTB_PRIM_XFORM(C.x);
+  if (xi != 0) {
+    DXform x = load_xform(xforms, xi);
+    o = xf_point(x, ray.o);
+    d = xf_vec(x, ray.d);
+  }
+  const float ix = rcp_fast(d.x), iy = rcp_fast(d.y), iz = rcp_fast(d.z);
+  const float tx0 = (A.x - o.x) * ix, tx1 = (B.x - o.x) * ix;
+  const float ty0 = (A.y - o.y) * iy, ty1 = (B.y - o.y) * iy;
+  const float tz0 = (A.z - o.z) * iz, tz1 = (B.z - o.z) * iz;
+  *t_enter = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fminf(tz0, tz1));
+  *t_exit = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fmaxf(tz0, tz1));
+  return *t_enter <= *t_exit;
+}
+
+// The reference restarts the boundary query at hit1.t + 0.0001 (src/medium.rs:31).  In f32 that increment is below one
+// ulp once |t| > 1024 and the second query would find the first surface again (a medium far from the ray origin
+// vanished: tests/field_checks.py build_far_medium), so the restart point is at least four ulps beyond hit1.t.
+RTB_DEV float medium_restart(float t1) { return t1 + fmaxf(0.0001f, fabsf(t1) * 4.8e-7f); }
+
 // ---- constant media: src/medium.rs:28-56 -------------------------------------------------------
 // Runs every medium against the ray after the surface query.  Per medium (reference order):
 // hit1 = boundary.hit(-MAX, MAX); hit2 = boundary.hit(hit1.t + 1e-4, MAX) — each the closest
@@ -442,7 +492,7 @@ __device__ __forceinline__ Surface finalize_hit(const SceneView& sv, const DPrim
 // Independent exponentials clipped to the running closest hit give the same distribution as
 // the reference's list scan (Q13).  Returns the index of the medium that scattered, or -1.
 template <bool kStats>
-__device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray, float t_min, float* t_closest,
+RTB_DEV int sample_media(const SceneView& sv, const RayF& ray, float t_min, float* t_closest,
                                             float xi0, float xi1, uint64_t seed, uint32_t pixel, uint32_t sample,
                                             uint32_t depth, Counters* cnt) {
   // xi0, xi1: the free-flight draws of media 0 and 1 (slots d, e of the bounce block); media
@@ -479,11 +529,16 @@ __device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray
       float disc = fmaf(A.w, A.w, -dot(l, l));
       float h = sqrt_fast(fmaxf(disc, 0.0f) * inv_a);
       t1 = tc - h, t2 = tc + h;
-      ok = disc > 0.0f && t2 > t1 + 0.0001f;
+      ok = disc > 0.0f && t2 > medium_restart(t1);
+    } else if (count == 1 && RTB_PRIM_TYPE(C0.x) == DP_BOX) {
+      // a Cube boundary (cornell_smoke): entry and exit face of one slab pass; the second query accepts
+      // t >= hit1.t + 1e-4 (Rect bounds are inclusive, src/rect.rs:46)
+      if (kStats) cnt->prim_tests += 2;
+      ok = box_interval(sv.bprims, first, C0, sv.xforms, ray, &t1, &t2) && t2 >= medium_restart(t1);
     } else {
 #pragma unroll 1
     for (int pass = 0; pass < 2 && ok; ++pass) {
-      const float lo = pass == 0 ? -CUDART_INF_F : t1 + 0.0001f;
+      const float lo = pass == 0 ? -CUDART_INF_F : medium_restart(t1);
       float best = CUDART_INF_F;
       bool any = false;
       for (int i = 0; i < count; ++i) {
@@ -514,7 +569,7 @@ __device__ __forceinline__ int sample_media(const SceneView& sv, const RayF& ray
 }
 
 // ---- textures: src/texture.rs, src/perlin.rs --------------------------------------------------
-__device__ __forceinline__ float perlin_noise(const DPerlin* __restrict__ P, V3f p) {  // src/perlin.rs:76-97
+RTB_DEV float perlin_noise(const DPerlin* __restrict__ P, V3f p) {  // src/perlin.rs:76-97
   float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
   float u = p.x - fx, v = p.y - fy, w = p.z - fz;
   // `floor(x) as usize`: negatives (and NaN) saturate to 0 (Q18); large values wrap with & 255
@@ -543,7 +598,7 @@ __device__ __forceinline__ float perlin_noise(const DPerlin* __restrict__ P, V3f
   return accum;
 }
 
-__device__ __forceinline__ float perlin_turb(const DPerlin* __restrict__ P, V3f p) {  // src/perlin.rs:99-109, depth 7
+RTB_DEV float perlin_turb(const DPerlin* __restrict__ P, V3f p) {  // src/perlin.rs:99-109, depth 7
   float accum = 0.0f, weight = 1.0f;
 #pragma unroll 1
   for (int d = 0; d < 7; ++d) {
@@ -560,10 +615,10 @@ struct TexCounters {
 
 // sign(sin(10 x)) == parity of floor(10 x / pi): the checker only needs the sign of the
 // product of three sines (src/texture.rs:41-42)
-__device__ __forceinline__ int sin10_negative(float x) { return ((int)floorf(x * 3.1830988618379067f)) & 1; }
+RTB_DEV int sin10_negative(float x) { return ((int)floorf(x * 3.1830988618379067f)) & 1; }
 
 template <bool kStats>
-__device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p, TexCounters* tc) {
+RTB_DEV V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p, TexCounters* tc) {
   for (;;) {
     // both halves of the 32-byte record at once: the colour load does not wait for the type test
     const int4 hd = __ldg(reinterpret_cast<const int4*>(sv.texs + tex));
@@ -595,13 +650,13 @@ __device__ __forceinline__ V3f texture_value(const SceneView& sv, int tex, float
 }
 
 // ---- materials: src/material.rs ------------------------------------------------------------------
-__device__ __forceinline__ V3f reflect(V3f v, V3f n) { return v - (2.0f * dot(v, n)) * n; }  // :9-11
+RTB_DEV V3f reflect(V3f v, V3f n) { return v - (2.0f * dot(v, n)) * n; }  // :9-11
 
 // Material::scatter.  Returns false when the path ends (DiffuseLight, absorbed Metal).
 // On success `ray` becomes the scattered ray (origin = hit.p, same time) and *atten the albedo.
 // rnd: the four draws of this bounce (ball x3, schlick).
 template <bool kStats>
-__device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int mat_tex, float mat_param, const Surface& s,
+RTB_DEV bool scatter(const SceneView& sv, int mat_type, int mat_tex, float mat_param, const Surface& s,
                                         RayF& ray, const Rand5& rnd, V3f* atten, TexCounters* tc) {
   if (mat_type == RTB_MAT_DIFFUSE_LIGHT) return false;  // :144-146
   if (mat_type == RTB_MAT_DIELECTRIC) {                 // :106-126
@@ -657,7 +712,7 @@ __device__ __forceinline__ bool scatter(const SceneView& sv, int mat_type, int m
 // Material::scatter without the albedo lookup (the caller evaluates the material's texture once
 // for both `emitted` and the attenuation): returns false when the path ends, else `ray` becomes
 // the scattered ray.  Same arithmetic as scatter() above.
-__device__ __forceinline__ bool scatter_dir(int mat_type, float mat_param, const Surface& s, RayF& ray, const Rand5& rnd) {
+RTB_DEV bool scatter_dir(int mat_type, float mat_param, const Surface& s, RayF& ray, const Rand5& rnd) {
   if (mat_type == RTB_MAT_DIFFUSE_LIGHT) return false;  // src/material.rs:144-146
   if (mat_type == RTB_MAT_DIELECTRIC) {                 // :106-126
     const float ref_idx = mat_param;
@@ -711,7 +766,7 @@ __device__ __forceinline__ bool scatter_dir(int mat_type, float mat_param, const
 // at src/util.rs:15-24; skipped iff lens_radius == 0 (src/camera.rs:54).  The time draw always
 // happens, as upstream (src/camera.rs:61).
 template <class Seed>  // uint64_t seed, or the PhiloxKeys made from it
-__device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, const Seed& seed, uint32_t pixel,
+RTB_DEV RayF camera_ray(const DCamera& cam, int i, int j, int nx, int ny, const Seed& seed, uint32_t pixel,
                                            uint32_t sample) {
   const Rand5 r5 = rand5(seed, 0u, pixel, sample, RTB_RNG_CAMERA);
   const float ju = r5.a, jv = r5.b, lr = r5.c, lp = r5.d, xt = r5.e;
@@ -735,7 +790,7 @@ __device__ __forceinline__ RayF camera_ray(const DCamera& cam, int i, int j, int
   return ray;
 }
 
-__device__ __forceinline__ V3f background_color(int background, V3f d) {
+RTB_DEV V3f background_color(int background, V3f d) {
   if (background == 1) {  // the gradient commented out at src/color.rs:18-20 (lit variant only)
     float inv = rsqrt_fast(dot(d, d));
     float t = 0.5f * (d.y * inv + 1.0f);

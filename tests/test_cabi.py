@@ -187,3 +187,60 @@ def test_philox_known_answers(rtb):
             (0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1))]
     for ctr, key, want in kat:
         assert rtb.philox4x32_10(ctr, key) == want
+
+
+def test_deserialize_rejects_hostile_scene_files(rtb):
+    """rtb_scene_deserialize / rtb_scene_load take arbitrary bytes (include/rtb_scene_format.h): every malformed record that
+    could hang or fault a later stage is refused here — self-referencing or forward-referencing checkers (flatten's
+    tex_needs_uv recursion, the device's texture_value loop), unknown texture / material types (the device falls through to
+    the image branch), bad Rect plane / Rotate axis selectors, image extents outside the pool, counts that wrap the size sum."""
+    import struct
+    s = rtb.Scene()
+    t_a, t_b = s.solid(0.1, 0.2, 0.3), s.solid(0.9, 0.9, 0.9)
+    t_c = s.checker(t_a, t_b)
+    t_i = s.image(np.zeros((4, 4, 3), np.uint8))
+    m = s.lambertian(t_c)
+    m2 = s.lambertian(t_i)
+    r = s.rect(rtb.PLANE_XY, 0, 0, 1, 1, 0.5, m)
+    w = s.list([s.rotate(rtb.AXIS_Y, r, 10.0), s.sphere((0, 0, 0), 1.0, m2)])
+    good = s.serialize()
+    assert rtb.Scene.deserialize(good) is not None
+    HDR, TEX, MAT, OBJ = 40, 48, 16, 112
+    n_tex, n_mat = struct.unpack_from("<II", good, 8)
+    tex_off = lambda i: HDR + i * TEX
+    mat_off = lambda i: HDR + n_tex * TEX + i * MAT
+    obj_off = lambda i: HDR + n_tex * TEX + n_mat * MAT + i * OBJ
+
+    def broken(off, fmt, *vals):
+        b = bytearray(good)
+        struct.pack_into(fmt, b, off, *vals)
+        return bytes(b)
+
+    cases = {
+        "checker references itself": broken(tex_off(t_c) + 4, "<i", t_c),
+        "checker references a later texture": broken(tex_off(t_c) + 8, "<i", t_i),
+        "unknown texture type": broken(tex_off(t_a), "<i", 7),
+        "negative texture type": broken(tex_off(t_a), "<i", -1),
+        "image nx beyond the pool": broken(tex_off(t_i) + 4, "<i", 1 << 20),
+        "image offset beyond the pool": broken(tex_off(t_i) + 16, "<Q", 1 << 60),
+        "image nx*ny overflows": broken(tex_off(t_i) + 4, "<ii", 0x7FFFFFFF, 0x7FFFFFFF),
+        "unknown material type": broken(mat_off(m), "<i", 9),
+        "rect plane selector": broken(obj_off(r) + 12, "<i", 3),
+        "rotate axis selector": broken(obj_off(r + 1) + 12, "<i", -1),
+        "image byte count wraps the size sum": broken(32, "<Q", 0xFFFFFFFFFFFFFF00),
+        "huge object count": broken(16, "<I", 0xFFFFFFFF),
+    }
+    for what, blob in cases.items():
+        with pytest.raises(rtb.RtbError):
+            rtb.Scene.deserialize(blob)
+    # random byte flips never crash: each either loads (and then flattens / counts without fault) or is refused
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        b = bytearray(good)
+        for _ in range(rng.integers(1, 6)):
+            b[rng.integers(8, len(b))] = rng.integers(0, 256)
+        try:
+            s2 = rtb.Scene.deserialize(bytes(b))
+        except rtb.RtbError:
+            continue
+        s2.prim_count(w)

@@ -94,36 +94,45 @@ def test_kat_committed_renders_reproduced_byte_for_byte(rtb, fname):
 
 
 # ---- 4. images: noise-floor-relative PSNR against the oracle ---------------------------------------------
+# "raise spp / lower resolution for the parity run until the floor permits 40 dB": sizes and sample
+# counts below put the oracle-vs-oracle floor at 43-51 dB on every scene (calibrated with the oracle, tools/parity_report.py),
+# so the north_star criterion (>= 40 dB against the reference render at matched spp) is asserted unconditionally.
 IMAGE_CASES = [
     # name, background, nx, ny, spp
-    ("two_spheres", 1, 200, 112, 256),
-    ("random_scene", 1, 160, 90, 128),
-    ("two_perlin_sphere", 1, 160, 90, 128),
-    ("earth", 1, 160, 90, 128),
-    ("simple_light", 0, 96, 54, 512),
-    ("cornell_box", 0, 64, 64, 2048),
-    ("cornell_smoke_book", 0, 64, 64, 1024),
-    ("final_scene_lit", 0, 64, 64, 512),
+    ("two_spheres", 1, 48, 27, 3072),
+    ("random_scene", 1, 48, 27, 2048),
+    ("two_perlin_sphere", 1, 48, 27, 2048),
+    ("earth", 1, 48, 27, 1024),
+    ("simple_light", 0, 48, 27, 24576),
+    ("cornell_box", 0, 32, 32, 65536),
+    ("cornell_smoke_book", 0, 32, 32, 40960),
+    ("final_scene_lit", 0, 32, 32, 49152),
 ]
+HI_FACTOR = 16
+
+
+def image_case_report(rtb, orc, name, bg, nx, ny, ns, nthreads=NT):
+    """One row of profiles/r2_parity.md: two oracle renders (the noise floor), the GPU at the same spp and at 16x."""
+    s, w, cam = rtb.Scene.named(name, nx, ny)
+    o = orc.OracleScene(s.serialize(), w)
+    a, _, _ = o.render(cam, nx, ny, ns, background=bg, seed=101, nthreads=nthreads)
+    b, _, _ = o.render(cam, nx, ny, ns, background=bg, seed=202, nthreads=nthreads)
+    g_sum, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=7), want_rgb8=False)
+    hi = HI_FACTOR * ns
+    h_sum, _, _ = s.render(w, cam, nx, ny, hi, rtb.default_opts(background=bg, seed=9), want_rgb8=False)
+    return image_parity(g_sum / ns, h_sum / hi, a, b, hi_factor=HI_FACTOR)
 
 
 @pytest.mark.parametrize("name,bg,nx,ny,ns", IMAGE_CASES)
 def test_image_matches_oracle_within_noise_floor(rtb, orc, name, bg, nx, ny, ns):
-    s, w, cam = rtb.Scene.named(name, nx, ny)
-    o = orc.OracleScene(s.serialize(), w)
-    a, _, _ = o.render(cam, nx, ny, ns, background=bg, seed=101, nthreads=NT)
-    b, _, _ = o.render(cam, nx, ny, ns, background=bg, seed=202, nthreads=NT)
-    g_sum, _, _ = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=7), want_rgb8=False)
-    hi = 16 * ns
-    h_sum, _, _ = s.render(w, cam, nx, ny, hi, rtb.default_opts(background=bg, seed=9), want_rgb8=False)
-    r = image_parity(g_sum / ns, h_sum / hi, a, b)
-    print(name, {k: (round(v, 2) if isinstance(v, float) else [round(x, 4) for x in v]) for k, v in r.items()})
+    r = image_case_report(rtb, orc, name, bg, nx, ny, ns)
+    print(name, {k: (round(v, 2) if isinstance(v, float) else [round(x, 5) for x in v]) for k, v in r.items()})
+    assert r["floor_db"] >= 40.5, r                        # the case is sized so that 40 dB is measurable
+    assert r["gpu_db"] >= 40.0, r                          # north_star: >= 40 dB PSNR against the reference render at matched spp
     assert r["gpu_db"] >= r["floor_db"] - 0.5, r          # as good as a second oracle run
     assert r["bias_db"] >= r["floor_db"] + 4.0, r         # and unbiased: ~ +6 dB when GPU noise vanishes
-    if r["floor_db"] >= 40.5:
-        assert r["gpu_db"] >= 40.0, r                      # >= 40 dB where the floor permits (north_star)
-    for c in range(3):
-        assert abs(r["mean_ratio"][c] - 1.0) < 0.02, r
+    for c in range(3):                                     # mean radiance within 3 sigma (plus 5e-4 of f32 arithmetic)
+        assert abs(r["mean_ratio"][c] - 1.0) <= 3.0 * r["mean_ratio_sigma"][c] + 5e-4, r
 
 
 def test_high_spp_image_reaches_40db(rtb, orc):
