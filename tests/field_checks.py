@@ -70,7 +70,9 @@ def check_hit_records(backend_scene, oracle_scene, world, rays, tol_scale=1.0):
     if not both.any():
         return out
     a, b = rec_ref[both], rec_dev[both].astype(np.float64)
-    scale = np.maximum(1.0, np.abs(a[:, 3:6]).max(axis=1))
+    # p = o + t*d: its round-off scales with the longer of |p| and the ray length t*|d|
+    ray_len = np.abs(a[:, 0:1] * rays[both, 3:6]).max(axis=1)
+    scale = np.maximum(1.0, np.maximum(np.abs(a[:, 3:6]).max(axis=1), ray_len))
     rel_t = np.abs(a[:, 0] - b[:, 0]) / np.maximum(np.abs(a[:, 0]), 1e-3)
     dp = np.abs(a[:, 3:6] - b[:, 3:6]).max(axis=1) / scale
     dn = np.abs(a[:, 6:9] - b[:, 6:9]).max(axis=1)

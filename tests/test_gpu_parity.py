@@ -32,6 +32,7 @@ def test_closest_hit_ids_agree_with_oracle(rtb, orc, name):
     p_ref, t_ref = o.closest_hit(rays, media=False)
     p_gpu, t_gpu = s.closest_hit(w, rays)
     agree = float((p_ref == p_gpu).mean())
+    print(name, {"primary_rays": int(rays.shape[0]), "primary_agree": agree, "primary_hit_frac": float((p_ref >= 0).mean())})
     assert agree >= 0.9999, f"{name}: {agree:.6f}"
     both = (p_ref == p_gpu) & (p_ref >= 0)
     if both.any():

@@ -168,7 +168,7 @@ void emu_camera_rays(const RtbCamera* c, int nx, int ny, int sidx, uint64_t seed
 // checks of the f32 path without a GPU).  out_sum: 3*nx*ny floats (SUM of samples); stats: [0] segments, [1] node steps,
 // [2] prim tests.
 void emu_render(void* p, const RtbCamera* c, int nx, int ny, int ns, int max_depth, double t_min_d, int background, uint64_t seed,
-                int nthreads, float* out_sum, uint64_t* stats) {
+                int nthreads, float* out_sum, uint64_t* stats, float* seg_dump, size_t seg_cap) {
   EmuScene* e = (EmuScene*)p;
   const SceneView& sv = e->view;
   DCamera cam;
@@ -177,6 +177,7 @@ void emu_render(void* p, const RtbCamera* c, int nx, int ny, int ns, int max_dep
   const float t_min = (float)t_min_d;
   std::atomic<int> next_row{0};
   std::atomic<uint64_t> a_seg{0}, a_node{0}, a_prim{0};
+  std::atomic<size_t> dump_n{0};  // seg_dump (optional): every segment's {o, d, time, self_prim, self_face}, 9 floats
   auto worker = [&]() {
     Counters cnt = {0, 0, 0};
     TexCounters tc = {{0, 0, 0, 0}};
@@ -192,6 +193,14 @@ void emu_render(void* p, const RtbCamera* c, int nx, int ny, int ns, int max_dep
           V3f thr = mk(1.f, 1.f, 1.f);
           int self_prim = -1, self_face = 0;
           for (int depth = 0;; ) {
+            if (seg_dump) {
+              const size_t k = dump_n.fetch_add(1);
+              if (k < seg_cap) {
+                float* q = seg_dump + 9 * k;
+                q[0] = ray.o.x, q[1] = ray.o.y, q[2] = ray.o.z, q[3] = ray.d.x, q[4] = ray.d.y, q[5] = ray.d.z, q[6] = ray.time;
+                q[7] = (float)self_prim, q[8] = (float)self_face;
+              }
+            }
             Hit best = trace_closest<true>(sv, ray, t_min, self_prim, self_face, &cnt);
             ++segs;
             const Rand5 rnd = rand5(keys, (uint32_t)depth, pixel, (uint32_t)smp, RTB_RNG_BOUNCE);

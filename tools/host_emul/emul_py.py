@@ -28,7 +28,8 @@ lib.emu_closest_hit_ex.argtypes = [_vp, _vp, _sz, _d, _vp, _vp, _vp, _vp]
 lib.emu_scatter.argtypes = [_vp, _i, _vp, _sz, _u64, _vp]
 lib.emu_sample.argtypes = [_i, _u64, _sz, _vp]
 lib.emu_camera_rays.argtypes = [_vp, _i, _i, _i, _u64, _vp]
-lib.emu_render.argtypes = [_vp, _vp, _i, _i, _i, _i, _d, _i, _u64, _i, _vp, _vp]
+lib.emu_render.argtypes = [_vp, _vp, _i, _i, _i, _i, _d, _i, _u64, _i, _vp, _vp, _vp, _sz]
+lib.emu_wide_stats.argtypes = [_vp, _vp, _sz, _i, _i, _vp]
 
 
 class EmuScene:
@@ -62,12 +63,22 @@ class EmuScene:
         lib.emu_scatter(self._p, mat, q.ctypes.data, q.shape[0], seed, out.ctypes.data)
         return out
 
-    def render(self, cam, nx, ny, ns, max_depth=50, t_min=1e-3, background=0, seed=1, nthreads=None):
+    def render(self, cam, nx, ny, ns, max_depth=50, t_min=1e-3, background=0, seed=1, nthreads=None, dump_segments=0):
         out = np.empty((ny, nx, 3), np.float32)
         st = np.zeros(3, np.uint64)
+        dump = np.zeros((dump_segments, 9), np.float32) if dump_segments else None
         lib.emu_render(self._p, C.addressof(cam), nx, ny, ns, max_depth, t_min, background, seed, nthreads or os.cpu_count() or 1,
-                       out.ctypes.data, st.ctypes.data)
-        return out, {"segments": int(st[0]), "node_tests": int(st[1]), "prim_tests": int(st[2])}
+                       out.ctypes.data, st.ctypes.data, dump.ctypes.data if dump_segments else None, dump_segments)
+        d = {"segments": int(st[0]), "node_tests": int(st[1]), "prim_tests": int(st[2])}
+        if dump_segments:
+            d["rays"] = dump[: min(dump_segments, d["segments"])]
+        return out, d
+
+    def wide_stats(self, rays9, width, mode):
+        r = np.ascontiguousarray(rays9, dtype=np.float32)
+        out = np.zeros(16, np.uint64)
+        lib.emu_wide_stats(self._p, r.ctypes.data, r.shape[0], width, mode, out.ctypes.data)
+        return out
 
 
 def device_camera_rays(cam, nx, ny, sample=0, seed=1, device=0):
