@@ -35,7 +35,9 @@ UNIT = "Mpaths/s"
 COST = {
     "node_test": 24.0,     # two AABB slab tests with precomputed 1/d (a9: 12 each)
     "prim_test": 20.0,     # sphere test (a11); rect 10, moving sphere 25, cube face scan more — 20 as the mean
-    "medium_test": 52.0,   # two boundary tests + interval + free flight (a17: 2 x 20 + 12)
+    "medium_test": 12.0,   # interval clamps + free flight of one medium (a17: "2 x boundary + 12"); its two boundary queries are
+                           # counted by the kernels as primitive tests (render.cu sample_media_const, trace.cuh sample_media) and
+                           # priced there — r1 priced them here as well (52), a double count the r1 verdict caught
     "shade": [15.0, 25.0, 45.0, 2.0, 8.0],   # lambertian, metal, dielectric, diffuse_light, isotropic (a18)
     "tex": [0.0, 30.0, 645.0, 10.0],         # solid, checker, noise, image (a19/a20)
     "hit_record": 9.0,     # p / normal finalisation per surface segment
@@ -196,27 +198,73 @@ def run_gpu(args):
     dev = torch.device("cuda", local)
     pipe = {"auto": rtb.PIPE_AUTO, "mega": rtb.PIPE_MEGAKERNEL, "wavefront": rtb.PIPE_WAVEFRONT}[args.pipeline]
     spp = args.spp_per_step
+    bands = args.shard == "bands"
+    # weak scaling: every rank renders `spp` samples of every pixel per step (spp sharding), or — row-band sharding —
+    # spp * world samples of its 1/world of the rows: the same number of paths per rank per step either way
     ns_total = spp * world  # samples per pixel rendered by one step across all ranks
 
     scene, w, cam = rtb.Scene.named(SCENE, NX, NY)
     scene.upload(w, local)
-    reducer = None
-    if world > 1 and args.reduce == "p2p":
-        # accumulation buffers owned by librtb200 and exported to rank 0: the exchange step is the
-        # fused P2P reduce + resolve kernel (csrc/peer.cu) instead of NCCL reduce + resolve
-        reducer = D.PeerReducer(NX, NY, local)
-        acc = reducer.acc
+    # ---- the exchange step (N > 1).  Default: sharded over the ranks through peer memory; --reduce picks another form
+    exchange_info = None
+    mode = args.reduce
+    ex = None
+    legacy = None
+    if world > 1:
+        if mode in ("auto", "p2p"):
+            try:
+                ex = D.ShardedExchange(NX, NY, local, mode="p2p")
+                mode = "p2p"
+            except Exception as e:  # no CUDA IPC between these ranks: NCCL carries the sharded exchange
+                if args.reduce == "p2p":
+                    raise
+                print(f"[bench] P2P exchange unavailable ({e}); using NCCL", file=sys.stderr)
+                mode = "nccl"
+            ok = torch.tensor([1 if ex is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok) == 0 and mode == "p2p":
+                if ex is not None:
+                    ex.close()
+                ex, mode = None, "nccl"
+        if mode == "nccl":
+            ex = D.ShardedExchange(NX, NY, local, mode="nccl")
+        if mode == "p2p-root":
+            legacy = D.PeerReducer(NX, NY, local)
+    if ex is not None:
+        acc, rgb8 = ex.acc, ex.rgb8
+    elif legacy is not None:
+        acc = legacy.acc
+        rgb8 = torch.empty(NY, NX, 3, dtype=torch.uint8, device=dev)
     else:
         acc = torch.zeros(NY, NX, 3, dtype=torch.float32, device=dev)
-    rgb8 = torch.empty(NY, NX, 3, dtype=torch.uint8, device=dev)
+        rgb8 = torch.empty(NY, NX, 3, dtype=torch.uint8, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
 
+    def set_shard(opts, k):
+        if bands:  # all ns_total samples of step k, on this rank's 4-row bands
+            opts.sample_begin, opts.sample_stride = k * ns_total, 1
+            opts.band_begin, opts.band_stride = rank, world
+        else:      # step k renders samples [k*ns_total, (k+1)*ns_total) of the image; rank r takes r, r+world, ...
+            opts.sample_begin, opts.sample_stride = k * ns_total + rank, world
+            opts.band_begin, opts.band_stride = 0, 1
+
     def step(k, opts):
-        # step k renders samples [k*ns_total, (k+1)*ns_total) of the image; rank r takes r, r+world, ...
-        opts.sample_begin = k * ns_total + rank
-        opts.sample_stride = world
+        set_shard(opts, k)
         return scene.render_device(cam, NX, NY, (k + 1) * ns_total, opts, acc.data_ptr(), stream)
+
+    def exchange(ns_done):
+        """Closes the image on rank 0: the path's one exchange step + quantisation.  Returns kernels launched by this rank."""
+        if ex is not None:
+            (ex.gather_bands if bands else ex.reduce_resolve)(ns_done, stream)
+            return 1
+        if legacy is not None:
+            legacy.reduce_resolve(ns_done, rgb8, stream=stream)
+            return 1 if rank == 0 else 0
+        if world > 1:  # "nccl-root": sum-reduce of whole buffers to rank 0, then resolve there (the r1 form)
+            D.reduce_accumulators(acc, dst=0)
+        rtb.resolve_device(acc.data_ptr(), NX, NY, ns_done, rgb8.data_ptr(), stream)
+        return 1
 
     opts = rtb.default_opts(pipeline=pipe, device=local)
     for k in range(args.warmup):
@@ -225,10 +273,12 @@ def run_gpu(args):
 
     # instrumented (untimed) pass of one step: operation counts for the work model + launch count
     so = rtb.default_opts(pipeline=pipe, device=local, collect_stats=1)
-    so.sample_begin, so.sample_stride = rank, world
+    set_shard(so, 0)
     st = scene.render_device(cam, NX, NY, ns_total, so, acc.data_ptr(), stream, want_stats=True)
     launches_per_step = st["kernel_launches"]
     work_per_step = algorithmic_lane_instr(st)
+    acc.zero_()
+    exchange(ns_total)  # warm-up of the exchange path (first-use costs: NCCL channels, peer mappings)
     acc.zero_()
 
     if world > 1:
@@ -242,37 +292,89 @@ def run_gpu(args):
             step(k, opts)
             ev[k][1].record()
         ev[-1][0].record()
-        if reducer is not None:  # the path's one exchange step, fused with the resolve, over peer memory
-            reducer.reduce_resolve(max(1, args.steps * ns_total), rgb8, stream=stream)
-        else:
-            if world > 1:  # the exchange step: sum-reduce of the accumulation buffers to rank 0 (NCCL)
-                D.reduce_accumulators(acc, dst=0)
-            rtb.resolve_device(acc.data_ptr(), NX, NY, max(1, args.steps * ns_total), rgb8.data_ptr(), stream)
-        ev[-1][1].record()
+        exchange_launches = exchange(max(1, args.steps * ns_total))
+        ev[-1][1].record()  # recorded after exchange() returned, i.e. after its closing host barrier
         torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     step_ms = [a.elapsed_time(b) for a, b in ev[:-1]]
     tail_ms = ev[-1][0].elapsed_time(ev[-1][1])
+    # (the P2P exchange contains host barriers: its closing event is recorded after exchange() returns, so the event pair
+    # brackets them; on a rank that finished its steps early the tail includes waiting for the slowest rank)
     total_ms = torch.tensor([sum(step_ms) + tail_ms], dtype=torch.float64, device=dev)
     kern_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    xch_ms = torch.tensor([tail_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(kern_ms, op=dist.ReduceOp.MAX)
-    total_ms, kern_ms = float(total_ms), float(kern_ms)
+        dist.all_reduce(xch_ms, op=dist.ReduceOp.MAX)
+    total_ms, kern_ms, xch_ms = float(total_ms), float(kern_ms), float(xch_ms)
     paths_per_step_rank = NX * NY * spp
     value = world * args.steps * paths_per_step_rank / (total_ms * 1e-3) / 1e6
+    final8 = rgb8.clone() if rank == 0 else None
 
-    # ---- e2e: the host-buffer C-ABI call (rtb_render): scene flatten + upload, render, D2H of the image
+    # ---- exchange self-check (N > 1): the P2P and the NCCL forms of the sharded exchange, and the r1 root reduce, give the
+    # same image from the same partial sums (<= 1 LSB: float addition order) — run inside the driver's own invocation
+    if world > 1:
+        exchange_info = {"mode": ("bands-" if bands else "") + mode, "ms": xch_ms}
+        if not bands:
+            try:
+                ns_chk = max(1, args.steps * ns_total)
+                keep = acc.clone()
+                imgs = {}
+                for m2 in ("p2p", "nccl"):
+                    if ex is not None and m2 == mode:
+                        imgs[m2] = final8
+                        continue
+                    try:
+                        e2 = D.ShardedExchange(NX, NY, local, mode=m2)
+                    except Exception as e:
+                        e2 = None
+                        print(f"[bench] exchange_check: {m2} unavailable: {e}", file=sys.stderr)
+                    okf = torch.tensor([1 if e2 is not None else 0], device=dev)
+                    dist.all_reduce(okf, op=dist.ReduceOp.MIN)
+                    if int(okf) == 0:
+                        if e2 is not None:
+                            e2.close()
+                        continue
+                    e2.acc.copy_(keep)
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    e2.reduce_resolve(ns_chk, stream)
+                    torch.cuda.synchronize()
+                    exchange_info[f"{m2}_ms_checked"] = (time.perf_counter() - t0) * 1e3
+                    imgs[m2] = e2.rgb8.clone() if rank == 0 else None
+                    e2.close()
+                root_acc = keep.clone()
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                D.reduce_accumulators(root_acc, dst=0)
+                root8 = torch.empty_like(rgb8)
+                rtb.resolve_device(root_acc.data_ptr(), NX, NY, ns_chk, root8.data_ptr(), stream)
+                torch.cuda.synchronize()
+                exchange_info["nccl_root_ms_checked"] = (time.perf_counter() - t0) * 1e3
+                if rank == 0:
+                    worst = 0
+                    for m2, im in imgs.items():
+                        worst = max(worst, int((im.int() - root8.int()).abs().max()))
+                    exchange_info["exchange_check"] = "ok" if worst <= 1 and len(imgs) >= 1 else f"MISMATCH (max diff {worst})"
+                    exchange_info["forms_compared"] = sorted(imgs) + ["nccl-root"]
+                    exchange_info["max_lsb_diff"] = worst
+                del keep, root_acc
+            except Exception as e:
+                exchange_info["exchange_check"] = f"error: {e}"
+
+    # ---- e2e: ONE image on rank 0's host through the public API with host buffers, everything inside the timed region
+    blob = scene.serialize()
+    n_e2e = max(1, min(args.steps, 3))
     e2e = None
-    if rank == 0 or world > 1:
-        blob = scene.serialize()
+    if world == 1:
+        # the host-buffer C-ABI call (rtb_render): scene flatten + upload, render, D2H of the image
         t_e2e, h2d, d2h = 0.0, 0, 0
-        n_e2e = max(1, min(args.steps, 3))
         for k in range(-1, n_e2e):  # call -1 is an untimed warm-up (first-use costs of the library's per-device workspace)
             t0 = time.perf_counter()
             s2 = rtb.Scene.deserialize(blob)  # fresh handle: flatten + BVH build + H2D inside the timed call
-            o2 = rtb.default_opts(pipeline=pipe, device=local, sample_begin=rank, sample_stride=world)
+            o2 = rtb.default_opts(pipeline=pipe, device=local)
             # create_image returns the quantised image only (tests/test.rs:71-84): the result read back is rgb8
             g_sum, g8, _ = s2.render(w, cam, NX, NY, ns_total, o2, want_sum=False)
             dt_call = time.perf_counter() - t0
@@ -282,13 +384,47 @@ def run_gpu(args):
             h2d = s2.device_bytes() + 256  # scene tables + camera/params
             d2h = g8.nbytes
             del s2
-        t = torch.tensor([t_e2e / n_e2e], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * paths_per_step_rank / float(t) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+        e2e = {"value": paths_per_step_rank / (t_e2e / n_e2e) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h), "note": "rtb_render() on a fresh scene handle with host buffers: deserialize + flatten + BVH build + H2D, render, resolve, D2H of the rgb8 image (what create_image returns); host wall clock, mean of the calls after one untimed warm-up call"}
+    else:
+        # every rank: fresh scene handle from the host bytes -> flatten + BVH + H2D -> its shard of ONE ns_total-spp image ->
+        # the exchange -> rank 0 copies the combined rgb8 image to pinned host memory.  Timed from a barrier to a barrier.
+        host8 = torch.empty(NY, NX, 3, dtype=torch.uint8).pin_memory() if rank == 0 else None
+        t_e2e, h2d = 0.0, 0
+        for k in range(-1, n_e2e):
+            acc.zero_()
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            s2 = rtb.Scene.deserialize(blob)
+            s2.upload(w, local)
+            o2 = rtb.default_opts(pipeline=pipe, device=local)
+            set_shard(o2, 0)
+            s2.render_device(cam, NX, NY, ns_total, o2, acc.data_ptr(), stream)
+            exchange(ns_total)
+            if rank == 0:
+                host8.copy_(rgb8, non_blocking=True)
+            torch.cuda.synchronize()
+            dist.barrier()
+            dt_call = time.perf_counter() - t0
+            if rank == 0:
+                print(f"[bench] e2e image {k}: {dt_call * 1e3:.1f} ms" + (" (warm-up, not counted)" if k < 0 else ""), file=sys.stderr)
+            if k >= 0:
+                t_e2e += dt_call
+            h2d = s2.device_bytes() + 256
+            del s2
+        t = torch.tensor([t_e2e / n_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * paths_per_step_rank / float(t) / 1e6, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world,
+               "d2h_bytes_per_step": int(NX * NY * 3),
+               "note": f"one {ns_total}-spp 4K image on rank 0's pinned host buffer per call: on every rank a fresh scene handle from host bytes "
+                       "(deserialize + flatten + BVH build + H2D of the tables), its shard of the samples, the exchange step "
+                       f"({exchange_info['mode']}), D2H of the combined rgb8 image on rank 0; host wall clock from a barrier to a barrier, "
+                       "max over ranks, mean of the calls after one untimed warm-up call"}
 
     if rank != 0:
+        if ex is not None:
+            ex.close()
         if world > 1:
             dist.destroy_process_group()
         return
@@ -305,20 +441,29 @@ def run_gpu(args):
         "bound": "fp32_issue", "achieved": achieved, "peak": issue_peak, "unit": "Tlane-instr/s",
         "frac": achieved / issue_peak, "traffic": ncu_traffic_bytes(NX, NY, spp),
         "note": ("SURVEY.md §8(d): scene tables (<1 MB + 1.5 MB texture) stay in L1/L2, no dense contraction, so the bound is "
-                 "SM instruction issue: peak = lane-instructions/s measured on this device by an FFMA+LOP3 issue microbenchmark "
+                 "SM instruction issue: peak = lane-instructions/s measured on this device by an FFMA issue microbenchmark "
                  "(rtb_issue_peak; nominal SMs x 128 lanes x sampled SM clock alongside); achieved = algorithmic "
-                 "lane-instructions (fixed cost table x device op counters of one step) / kernel time. "
+                 "lane-instructions (fixed cost table x device op counters of one step; a medium's two boundary queries are "
+                 "priced once, as primitive tests) / kernel time. "
                  "MEASURED_PEAKS.json has no FP32 entry. traffic = dram bytes read + written by one launch of this "
-                 "workload (ncu, profiles/r1_mega_traffic_4k64.csv): megabytes against the algorithmic image + scene "
-                 "tables, i.e. HBM is idle; L2 sees 348 GB per launch (traversal-stack write-through)."),
+                 "workload (ncu): megabytes against the algorithmic image + scene tables, i.e. HBM is idle. "
+                 "hardware = the ncu view of the same launch shape (profiles/), not measured in this run."),
         "segments_per_path": st["segments"] / st["paths"], "node_tests_per_segment": st["node_tests"] / st["segments"],
         "prim_tests_per_segment": st["prim_tests"] / st["segments"],
         "lane_instr_per_segment_model": work_per_step / st["segments"],
         "Msegments_per_s": value * st["segments"] / st["paths"],
         "hbm_peak_gbs_measured": peaks.get("hbm_gbs"),
         "peak_nominal": nominal_peak, "peak_measured_fma_only": fma_peak, "peak_measured_fma_lop3": mixed_peak, "peak_measured_slab_mix": slab_peak,
+        "hardware": ncu_hardware_view(NX, NY, spp),
     }
     cpu_v, cpu_desc, cores, _ = cpu_reference_sample(seconds=args.cpu_seconds) if args.cpu_seconds > 0 else (None, "skipped", 0, 0)
+    # the reference's own threading model is ONE thread (tests/test.rs:28 `--test-threads=1`, Rc world src/bvh.rs:11-12)
+    cpu1_v, cpu1_desc, _, _ = cpu_reference_sample(seconds=min(8.0, args.cpu_seconds), nthreads=1) if args.cpu_seconds > 0 else (None, "skipped", 0, 0)
+    par = f"{'row-band' if bands else 'spp'}-shard x{world}"
+    if world > 1:
+        par += {"p2p": " + sharded P2P exchange (each GPU reduces 1/N of the image over NVLink, rgb8 slices land on rank 0)",
+                "nccl": " + NCCL reduce_scatter(sum) + per-slice resolve + gather of rgb8",
+                "p2p-root": " + fused P2P reduce+resolve on rank 0", "nccl-root": " + NCCL reduce(sum) to rank 0"}.get(mode, "")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -326,23 +471,41 @@ def run_gpu(args):
         "config": {"workload": f"{SCENE} as written (tests/test.rs:419-523), {NX}x{NY}, {spp} spp per step per GPU, max_depth 50, "
                                f"black background; 10k-spp image = {10000 // spp} steps; L2 flushed (256 MB write) between timed steps",
                    "pipeline": args.pipeline, "seconds_per_4k_10kspp_image": NX * NY * 10000 / (value * 1e6),
-                   "parallelism": f"spp-shard x{world}" + ((" + fused P2P reduce+resolve on rank 0" if reducer is not None
-                                                             else " + NCCL reduce(sum) to rank 0") if world > 1 else ""),
-                   "exchange_ms": tail_ms},
-        "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps + 1), "clocks": ck, "roofline": roofline,
-        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_desc},
+                   "parallelism": par, "exchange_ms": xch_ms},
+        "e2e": e2e, "gpu_launches": int(launches_per_step * args.steps + exchange_launches), "clocks": ck, "roofline": roofline,
+        "cpu_baseline": {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port", "sample": cpu_desc,
+                         "single_thread": {"value": cpu1_v, "unit": UNIT, "cores": 1, "sample": cpu1_desc,
+                                           "note": "the reference is single-threaded (tests/test.rs:28, src/bvh.rs:11-12): this is its own execution model"}},
     }
+    if exchange_info:
+        line["exchange"] = exchange_info
     sys.stdout.flush()
     os.write(json_fd, (json.dumps(line) + "\n").encode())
+    if ex is not None:
+        ex.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_hardware_view(nx, ny, spp):
+    """The ncu hardware counters of one k_render_mega launch of exactly this shape, from the committed summary
+    (profiles/r2_mega_hw_4k64.json, written by tools/ncu_summary.py from an `ncu --set full` capture); None otherwise."""
+    f = ROOT / "profiles" / "r2_mega_hw_4k64.json"
+    if (nx, ny, spp) != (3840, 2160, 64) or not f.exists():
+        return None
+    try:
+        return json.loads(f.read_text())
+    except Exception:
+        return None
 
 
 def ncu_traffic_bytes(nx, ny, spp):
     """dram__bytes_read.sum + dram__bytes_write.sum of one k_render_mega launch, from the committed ncu capture of
     exactly this launch shape (profiles/r1_mega_traffic_4k64.csv: 3840x2160, 64 spp); None for any other shape."""
     import csv
-    f = ROOT / "profiles" / "r1_mega_traffic_4k64.csv"
+    f = ROOT / "profiles" / "r2_mega_traffic_4k64.csv"
+    if not f.exists():
+        f = ROOT / "profiles" / "r1_mega_traffic_4k64.csv"
     if (nx, ny, spp) != (3840, 2160, 64) or not f.exists():
         return None
     per_launch = {}
@@ -359,7 +522,10 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--reduce", default="nccl", choices=["nccl", "p2p"], help="N>1 exchange step: NCCL reduce + resolve, or the fused P2P kernel")
+    ap.add_argument("--reduce", default="auto", choices=["auto", "p2p", "nccl", "p2p-root", "nccl-root"],
+                    help="N>1 exchange step: sharded over the ranks through peer memory (p2p; auto falls back to nccl), sharded over NCCL "
+                         "(reduce_scatter + resolve + gather), or the r1 forms that pull everything to rank 0")
+    ap.add_argument("--shard", default="spp", choices=["spp", "bands"], help="N>1 work split: samples per pixel (default) or 4-row image bands")
     ap.add_argument("--pipeline", default="auto", choices=["auto", "mega", "wavefront"])
     ap.add_argument("--spp-per-step", type=int, default=SPP_PER_STEP)
     ap.add_argument("--cpu-seconds", type=float, default=15.0)

@@ -134,8 +134,16 @@ typedef struct rtb_render_opts {
   int pipeline;        /* RtbPipeline */
   int device;          /* CUDA device ordinal */
   int collect_stats;   /* count segments / node tests / primitive tests (slower, untimed runs) */
+  int band_begin;      /* row-band sharding (the "image tiles" split of the pixel loop, tests/test.rs:62-63): this call */
+  int band_stride;     /* renders the 4-row bands b = band_begin + i*band_stride of the image; 0,1 (or 0,0) for all rows */
+  int multi_shard;     /* rtb_render_multi only: RtbMultiShard — how the call splits the work over its devices */
   int reserved[7];
 } rtb_render_opts;
+/* rtb_render_multi: RTB_SHARD_SAMPLES — device g renders samples g, g+G, ... of every pixel, one sum-reduce closes the
+ * image (best when there are many samples per pixel); RTB_SHARD_BANDS — device g renders every sample of the 4-row bands
+ * g, g+G, ...: disjoint pixels, no arithmetic in the exchange, only rgb8 rows move (best at low samples per pixel). */
+typedef enum RtbMultiShard { RTB_SHARD_SAMPLES = 0, RTB_SHARD_BANDS = 1 } RtbMultiShard;
+#define RTB_BAND_ROWS 4
 
 typedef struct rtb_stats {
   uint64_t paths, segments;
@@ -205,15 +213,29 @@ int rtb_peer_open(const void* handle64, int device, void** d_ptr);
 int rtb_peer_close(void* d_ptr);
 int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, int ny, int ns,
                               float* d_total, uint8_t* d_rgb8, void* cuda_stream);
+/* The SHARDED form of that exchange: the same kernel over the value range [first_value, first_value + n_values) of the
+ * full-size buffers (all pointers are BASE pointers; first_value a multiple of 4 keeps the 128-bit path).  With G ranks
+ * each calling it for its own 1/G of the image — d_sums = every rank's buffer (peer-mapped), d_rgb8 = the root's rgb8
+ * buffer (peer-mapped) — every GPU pulls (G-1)/G of ITS slice over NVLink instead of the root pulling G-1 whole images,
+ * and the quantised slice lands on the root directly. */
+int rtb_reduce_resolve_range_device(const float* const* d_sums, int n_bufs, size_t first_value, size_t n_values, int ns,
+                                    float* d_total, uint8_t* d_rgb8, void* cuda_stream);
+/* Row-band sharding (rtb_render_opts.band_begin / band_stride): quantise this shard's 4-row bands of d_sum_rgb (a
+ * full-size accumulation buffer).  compact == 0: into their place in a full-size rgb8 image — the caller's own or the
+ * root's peer-mapped one (the shards' bands tile the image, no arithmetic in the exchange); compact != 0: packed
+ * consecutively, band i of the shard at row 4i (for a gather). */
+int rtb_resolve_bands_device(const float* d_sum_rgb, int nx, int ny, int ns, int band_begin, int band_stride,
+                             uint8_t* d_rgb8, int compact, void* cuda_stream);
 
-/* create_image on several GPUs of this node from one call (csrc/multi.cu): one host thread per
- * device renders the sample slice s = i, i+G, ... of every pixel, then devices[0] sums the G
- * partial images over peer access and quantises them in one kernel (rtb_reduce_resolve_device).
- * devices == NULL: ordinals 0 .. n_devices-1 (n_devices <= 0: every visible device).  The image is
- * the one rtb_render produces for the same seed, whatever G is (the draws are counter-based), up
- * to the order of the float adds.  opts->device and the sample_begin/stride fields are ignored /
- * must be 0,1.  stats (optional): sums over the devices, device_ms = the slowest shard,
- * reserved[0] = G. */
+/* create_image on several GPUs of this node from one call (csrc/multi.cu): one host thread per device renders its
+ * shard — the sample slice s = i, i+G, ... of every pixel (opts->multi_shard = RTB_SHARD_SAMPLES, default) or every
+ * sample of the 4-row bands i, i+G, ... (RTB_SHARD_BANDS) — then the exchange runs sharded over the devices: device g
+ * sums + quantises 1/G of the pixels from all G partial images over peer access (band shards: quantises its own rows)
+ * and stores the result into devices[0]'s image, which goes to the host once.
+ * devices == NULL: ordinals 0 .. n_devices-1 (n_devices <= 0: every visible device).  The image is the one rtb_render
+ * produces for the same seed, whatever G is (the draws are counter-based: same sample set; sums equal up to the order
+ * of the float adds, <= 1 LSB after quantisation).  opts->device, sample_begin/stride and band_begin/stride are ignored /
+ * must be 0,1.  stats (optional): sums over the devices, device_ms = the slowest shard, reserved[0] = G. */
 int rtb_render_multi(rtb_scene*, int world, const RtbCamera*, int nx, int ny, int ns, const rtb_render_opts*,
                      const int* devices, int n_devices, float* out_sum_rgb, uint8_t* out_rgb8, rtb_stats*);
 

@@ -33,6 +33,8 @@ AXIS_X, AXIS_Y, AXIS_Z = 0, 1, 2
 BG_BLACK, BG_SKY = 0, 1
 BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
 PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_POOL, PIPE_DUAL = 0, 1, 2, 3, 4
+SHARD_SAMPLES, SHARD_BANDS = 0, 1
+BAND_ROWS = 4
 
 NAMED_SCENES = (
     "random_scene", "two_spheres", "two_perlin_sphere", "earth", "simple_light",
@@ -53,7 +55,8 @@ class RenderOpts(C.Structure):
     _fields_ = [
         ("max_depth", C.c_int), ("t_min", C.c_double), ("background", C.c_int), ("seed", C.c_uint64),
         ("sample_begin", C.c_int), ("sample_stride", C.c_int), ("pipeline", C.c_int), ("device", C.c_int),
-        ("collect_stats", C.c_int), ("reserved", C.c_int * 7),
+        ("collect_stats", C.c_int), ("band_begin", C.c_int), ("band_stride", C.c_int), ("multi_shard", C.c_int),
+        ("reserved", C.c_int * 7),
     ]
 
 
@@ -134,6 +137,8 @@ _sig("rtb_peer_export", _i, _vp, _vp)
 _sig("rtb_peer_open", _i, _vp, _i, C.POINTER(C.c_void_p))
 _sig("rtb_peer_close", _i, _vp)
 _sig("rtb_reduce_resolve_device", _i, C.POINTER(C.c_void_p), _i, _i, _i, _i, _vp, _vp, _vp)
+_sig("rtb_reduce_resolve_range_device", _i, C.POINTER(C.c_void_p), _i, _sz, _sz, _i, _vp, _vp, _vp)
+_sig("rtb_resolve_bands_device", _i, _vp, _i, _i, _i, _i, _i, _vp, _i, _vp)
 _sig("rtb_closest_hit", _i, _vp, _i, _vp, _sz, _d, _i, _vp, _vp)
 _sig("rtb_debug_texture_value", _i, _vp, _i, _i, _vp, _sz, _i, _vp)
 _sig("rtb_closest_hit_ex", _i, _vp, _i, _vp, _sz, _d, _vp, _i, _vp, _vp)
@@ -499,6 +504,20 @@ def reduce_resolve_device(sum_ptrs, nx, ny, ns, d_rgb8_ptr: int, d_total_ptr: in
     arr = (C.c_void_p * len(sum_ptrs))(*sum_ptrs)
     _h(lib.rtb_reduce_resolve_device(arr, len(sum_ptrs), nx, ny, ns, d_total_ptr or None, d_rgb8_ptr, stream or None),
        "reduce_resolve_device")
+
+
+def reduce_resolve_range_device(sum_ptrs, first_value, n_values, ns, d_rgb8_ptr: int, d_total_ptr: int = 0, stream: int = 0):
+    """The sharded exchange: sum + quantise values [first_value, first_value + n_values) of the full-size buffers in
+    `sum_ptrs` (base pointers) into the full-size rgb8 image at d_rgb8_ptr (base pointer, own or peer-mapped)."""
+    arr = (C.c_void_p * len(sum_ptrs))(*sum_ptrs)
+    _h(lib.rtb_reduce_resolve_range_device(arr, len(sum_ptrs), first_value, n_values, ns, d_total_ptr or None, d_rgb8_ptr,
+                                           stream or None), "reduce_resolve_range_device")
+
+
+def resolve_bands_device(d_sum_ptr: int, nx, ny, ns, band_begin, band_stride, d_rgb8_ptr: int, compact=False, stream: int = 0):
+    """Quantise this shard's 4-row bands of a full-size accumulation buffer (row-band sharding)."""
+    _h(lib.rtb_resolve_bands_device(d_sum_ptr, nx, ny, ns, band_begin, band_stride, d_rgb8_ptr, int(bool(compact)), stream or None),
+       "resolve_bands_device")
 
 
 def primary_rays(cam, nx, ny, sample=0, seed=1) -> np.ndarray:

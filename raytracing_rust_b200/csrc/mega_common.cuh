@@ -16,6 +16,7 @@ struct MegaParams {
   int sample_count;   // samples per pixel in this launch
   int slices;         // work items per pixel tile (each takes every slices-th sample of the launch)
   int n_items;        // tiles * slices; warps draw items from a global counter until none is left
+  int band_begin, band_stride;  // row-band sharding: tile row r of this launch is tile row band_begin + r * band_stride of the image
   int max_depth;
   float t_min;
   int background;

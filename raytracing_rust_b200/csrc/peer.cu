@@ -66,6 +66,23 @@ __global__ void __launch_bounds__(256) k_reduce_resolve(PeerBufs bufs, size_t n_
   }
 }
 
+// Row-band sharding: quantise the 4-row bands band_begin, band_begin + band_stride, ... of a full-size accumulation
+// buffer.  compact == 0: each row goes to its own place in a full-size rgb8 image (this GPU's or, through a peer-mapped
+// pointer, the root's: the bands of the G shards tile the image without overlap).  compact != 0: the shard's rows are
+// packed consecutively (for a gather).  One thread per value.
+__global__ void __launch_bounds__(256) k_resolve_bands(const float* __restrict__ sum, int nx, int ny, float inv_ns, int band_begin,
+                                                       int band_stride, int compact, size_t n_values, uint8_t* __restrict__ rgb8) {
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;  // index into the shard's packed rows
+  if (idx >= n_values) return;
+  const size_t row_len = (size_t)nx * 3;
+  const size_t lrow = idx / row_len, col = idx - lrow * row_len;
+  const size_t band = lrow / RTB_BAND_ROWS, r = lrow - band * RTB_BAND_ROWS;
+  const size_t row = ((size_t)band_begin + band * band_stride) * RTB_BAND_ROWS + r;
+  if (row >= (size_t)ny) return;
+  const size_t src = row * row_len + col;
+  rgb8[compact ? idx : src] = quantise(sum[src], inv_ns);
+}
+
 }  // namespace rtb
 
 using namespace rtb;
@@ -114,17 +131,26 @@ int rtb_peer_close(void* d_ptr) {
 
 int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, int ny, int ns, float* d_total, uint8_t* d_rgb8,
                               void* cuda_stream) {
-  if (!d_sums || n_bufs < 1 || n_bufs > RTB_MAX_PEER_BUFFERS || nx <= 0 || ny <= 0 || ns <= 0 || !d_rgb8)
+  if (nx <= 0 || ny <= 0) return fail(RTB_ERR_INVALID, "reduce_resolve_device: bad argument");
+  return rtb_reduce_resolve_range_device(d_sums, n_bufs, 0, (size_t)3 * nx * ny, ns, d_total, d_rgb8, cuda_stream);
+}
+
+int rtb_reduce_resolve_range_device(const float* const* d_sums, int n_bufs, size_t first_value, size_t n_values, int ns,
+                                    float* d_total, uint8_t* d_rgb8, void* cuda_stream) {
+  if (!d_sums || n_bufs < 1 || n_bufs > RTB_MAX_PEER_BUFFERS || ns <= 0 || !d_rgb8)
     return fail(RTB_ERR_INVALID, "reduce_resolve_device: bad argument");
+  if (n_values == 0) return RTB_OK;
+  d_rgb8 += first_value;
+  if (d_total) d_total += first_value;
   PeerBufs b;
   b.n = n_bufs;
-  bool vec = ((size_t)3 * nx * ny) % 4 == 0 && ((uintptr_t)d_rgb8 & 3) == 0 && (!d_total || ((uintptr_t)d_total & 15) == 0);
+  bool vec = n_values % 4 == 0 && ((uintptr_t)d_rgb8 & 3) == 0 && (!d_total || ((uintptr_t)d_total & 15) == 0);
   for (int g = 0; g < RTB_MAX_PEER_BUFFERS; ++g) {
-    b.p[g] = g < n_bufs ? d_sums[g] : nullptr;
+    b.p[g] = g < n_bufs && d_sums[g] ? d_sums[g] + first_value : nullptr;
     if (g < n_bufs && !d_sums[g]) return fail(RTB_ERR_INVALID, "reduce_resolve_device: null buffer");
-    if (g < n_bufs && ((uintptr_t)d_sums[g] & 15)) vec = false;
+    if (g < n_bufs && ((uintptr_t)b.p[g] & 15)) vec = false;
   }
-  const size_t n = (size_t)3 * nx * ny;
+  const size_t n = n_values;
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -134,6 +160,20 @@ int rtb_reduce_resolve_device(const float* const* d_sums, int n_bufs, int nx, in
     k_reduce_resolve<true><<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(b, n, 1.0f / (float)ns, d_total, d_rgb8);
   else
     k_reduce_resolve<false><<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(b, n, 1.0f / (float)ns, d_total, d_rgb8);
+  PEER_TRY(cudaGetLastError());
+  return RTB_OK;
+}
+
+int rtb_resolve_bands_device(const float* d_sum_rgb, int nx, int ny, int ns, int band_begin, int band_stride, uint8_t* d_rgb8,
+                             int compact, void* cuda_stream) {
+  if (!d_sum_rgb || !d_rgb8 || nx <= 0 || ny <= 0 || ns <= 0 || band_begin < 0 || band_stride < 1)
+    return fail(RTB_ERR_INVALID, "resolve_bands_device: bad argument");
+  const int bands_all = (ny + RTB_BAND_ROWS - 1) / RTB_BAND_ROWS;
+  const int my_bands = band_begin < bands_all ? (bands_all - band_begin + band_stride - 1) / band_stride : 0;
+  const size_t n = (size_t)my_bands * RTB_BAND_ROWS * nx * 3;
+  if (n == 0) return RTB_OK;
+  k_resolve_bands<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)cuda_stream>>>(d_sum_rgb, nx, ny, 1.0f / (float)ns, band_begin,
+                                                                                     band_stride, compact, n, d_rgb8);
   PEER_TRY(cudaGetLastError());
   return RTB_OK;
 }

@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           int4 info = make_int4(-1, 0, 0, 0);
           if (items_left) {
             const int tile = item / P.slices, slice = item - tile * P.slices;
-            const int x0 = (tile % tiles_x) * 8, y0 = (tile / tiles_x) * 4;
+            const int x0 = (tile % tiles_x) * 8, y0 = ((tile / tiles_x) * P.band_stride + P.band_begin) * 4;
             const int w_t = min(8, P.nx - x0), n_pix = w_t * min(4, P.ny - y0);
             const int my_count = slice < P.sample_count ? (P.sample_count - slice + P.slices - 1) / P.slices : 0;
             info = make_int4(x0, y0, w_t | (n_pix << 8), slice);
@@ -548,7 +548,12 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
   const int stride = std::max(1, o.sample_stride);
   const int begin = std::max(0, o.sample_begin);
   const int my_samples = begin < ns ? (ns - begin + stride - 1) / stride : 0;
-  const long long tiles = (long long)((nx + 7) / 8) * ((ny + 3) / 4);
+  // row-band sharding: this call owns the 4-row tile rows band_begin, band_begin + band_stride, ...
+  const int band_stride = std::max(1, o.band_stride), band_begin = std::max(0, o.band_begin);
+  const int bands_all = (ny + 3) / 4;
+  const int my_bands = band_begin < bands_all ? (bands_all - band_begin + band_stride - 1) / band_stride : 0;
+  const long long tiles = (long long)((nx + 7) / 8) * my_bands;
+  if (tiles == 0) return RTB_OK;
   // enough resident warps to fill the machine: split a pixel's samples over several threads
   // when the image alone does not supply ~2 waves of warps
   const long long want_warps = (long long)d->prop.multiProcessorCount * 64 * 2;
@@ -559,6 +564,7 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.sample_count = std::min(chunk_max, my_samples - done);
     P.sample_first = begin + done * stride;
     P.sample_step = stride;
+    P.band_begin = band_begin, P.band_stride = band_stride;
     int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
@@ -687,6 +693,10 @@ int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int
   }
   int pipe = opts->pipeline;
   if (pipe == RTB_PIPE_AUTO) pipe = RTB_PIPE_MEGAKERNEL;
+  if (opts->band_stride > 1 && pipe != RTB_PIPE_MEGAKERNEL)
+    return fail(RTB_ERR_INVALID, "render_device: row-band sharding is implemented by the megakernel pipeline only");
+  if (opts->band_begin < 0 || opts->band_stride < 0 || (opts->band_stride <= 1 && opts->band_begin > 0))
+    return fail(RTB_ERR_INVALID, "render_device: bad band_begin / band_stride");
   if (pipe == RTB_PIPE_POOL && !pool_supports(d)) pipe = RTB_PIPE_MEGAKERNEL;  // BVH deeper than the pool's stack
   if (pipe == RTB_PIPE_WAVEFRONT)
     rc = launch_wavefront(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
@@ -707,7 +717,12 @@ int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int
     std::memset(stats, 0, sizeof *stats);
     const int stride = std::max(1, opts->sample_stride), begin = std::max(0, opts->sample_begin);
     const uint64_t my_samples = begin < ns ? (uint64_t)(ns - begin + stride - 1) / stride : 0;
-    stats->paths = my_samples * (uint64_t)nx * ny;
+    uint64_t my_rows = (uint64_t)ny;
+    if (opts->band_stride > 1) {
+      my_rows = 0;
+      for (int b = opts->band_begin; b * RTB_BAND_ROWS < ny; b += opts->band_stride) my_rows += (uint64_t)std::min(RTB_BAND_ROWS, ny - b * RTB_BAND_ROWS);
+    }
+    stats->paths = my_samples * (uint64_t)nx * my_rows;
     stats->segments = h[1];
     stats->node_tests = h[2], stats->prim_tests = h[3], stats->medium_tests = h[4];
     for (int i = 0; i < 5; ++i) stats->shade[i] = h[5 + i];

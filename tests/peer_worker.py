@@ -36,4 +36,30 @@ if rank == 0:
     print("peer reduce ok", float(t.mean()), flush=True)
 dist.barrier()
 red.close()
+
+# ---- the sharded exchange (every rank reduces 1/G of the image) and row-band sharding, P2P and NCCL forms ----------------
+stream = torch.cuda.current_stream().cuda_stream
+if rank == 0:
+    ref8_t = torch.from_numpy(ref8).cuda()
+for mode in ("p2p", "nccl"):
+    ex = D.ShardedExchange(nx, ny, local, mode=mode)
+    D.render_sharded(scene, cam, nx, ny, ns, rtb.default_opts(device=local), ex.acc, rank, world, stream)
+    img = ex.reduce_resolve(ns, stream)
+    torch.cuda.synchronize()
+    if rank == 0:
+        d = (img.int() - ref8_t.int()).abs()
+        assert int(d.max()) <= 1 and float((d > 0).float().mean()) < 1e-3, (mode, int(d.max()))
+    dist.barrier()
+    ex.acc.zero_()
+    D.render_band_sharded(scene, cam, nx, ny, ns, rtb.default_opts(device=local), ex.acc, rank, world, stream)
+    img = ex.gather_bands(ns, stream)
+    torch.cuda.synchronize()
+    if rank == 0:
+        d = (img.int() - ref8_t.int()).abs()
+        assert int(d.max()) <= 1 and float((d > 0).float().mean()) < 1e-3, (mode, "bands", int(d.max()))
+    dist.barrier()
+    ex.close()
+if rank == 0:
+    print("sharded exchange ok", flush=True)
+dist.barrier()
 dist.destroy_process_group()

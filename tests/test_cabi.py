@@ -55,7 +55,7 @@ def test_cpp_host_api_builds_and_fails_loudly_without_a_gpu(rtb, tmp_path):
 def test_struct_layouts_match_ctypes(rtb):
     # sizes the Python mirror assumes (include/rtb200.h, rtb_scene_format.h)
     assert C.sizeof(rtb.RtbCamera) == 15 * 8
-    assert C.sizeof(rtb.RenderOpts) == 80
+    assert C.sizeof(rtb.RenderOpts) == 96
     assert C.sizeof(rtb.Stats) == (5 + 5 + 4 + 1) * 8 + 8 + 8 * 8
     o = rtb.default_opts()
     assert (o.max_depth, o.t_min, o.background, o.sample_stride) == (50, 1e-3, 0, 1)  # src/color.rs:7,9

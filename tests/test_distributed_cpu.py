@@ -25,6 +25,17 @@ def test_sample_partition_is_exact_cover():
         D.shard_samples(8, 2, 2)
 
 
+def test_row_band_partition_is_exact_cover():
+    for ny in (1, 3, 4, 5, 64, 117, 2160):
+        for world in (1, 2, 3, 8):
+            seen = []
+            for rank in range(world):
+                rows = D.shard_bands(ny, rank, world)
+                assert all((r // 4) % world == rank for r in rows)
+                seen += rows
+            assert sorted(seen) == list(range(ny))
+
+
 def test_resolve_host_matches_reference_quantisation():
     acc = np.array([[[0.0, 100.0, 25.0], [400.0, np.nan, -1.0]]])  # sums over ns = 100
     out = D.resolve_host(acc, 100)
