@@ -57,6 +57,17 @@ struct alignas(32) DNode {
   i4 n3;  // child0, child1 (>= 0 inner node index; < 0 leaf: ~v = first_prim << 3 | count, count 0..7), -, -
 };
 
+// Four-wide node (the two-child SAH tree collapsed by surface area, flatten.cpp): 128 bytes = three 256-bit loads of
+// plane coordinates (x, y, z: the four children's lo then hi) + one 128-bit load of child references.  About half the
+// traversal steps of the two-child tree for the same number of box tests (profiles/r2_experiments.txt).
+struct alignas(32) DNode4 {
+  float lox[4], hix[4];
+  float loy[4], hiy[4];
+  float loz[4], hiz[4];
+  int child[4];  // >= 0: DNode4 index; < 0: leaf code as in DNode; unused slots: an empty leaf (~0) behind a box no ray meets
+  int pad[4];
+};
+
 struct alignas(16) DXform {
   float m[9];  // row-major M:  local = M * world + b
   float b[3];
@@ -90,6 +101,7 @@ struct alignas(16) DMedium {
 // What the kernels see (passed by value as a kernel parameter).
 struct SceneView {
   const DNode* nodes;
+  const DNode4* nodes4;  // the same tree four-wide (nullptr when only the two-child tree exists: device-built LBVH)
   const DPrim* prims;    // surfaces, BVH leaf order
   const DPrim* bprims;   // medium boundaries
   const DMedium* media;
@@ -99,6 +111,7 @@ struct SceneView {
   const DPerlin* perlin;
   const uint32_t* texels;  // RGBA8
   int n_nodes, n_prims, n_media, root;  // root: node index (always an inner node)
+  int root4;                            // root of nodes4
 };
 
 struct DCamera {  // src/camera.rs:8-18, f32

@@ -329,6 +329,23 @@ void pad_box(const Box3& b, float lo[3], float hi[3]) {
 
 }  // namespace
 
+namespace {
+// a four-wide node whose only child is one leaf (or nothing): scenes with zero or one surface primitive
+DNode4 lone_leaf_node4(const float* lo, const float* hi, int leaf) {
+  const float far_away = 1e30f;
+  DNode4 dn{};
+  for (int k = 0; k < 4; ++k) {
+    dn.lox[k] = dn.hix[k] = dn.loy[k] = dn.hiy[k] = dn.loz[k] = dn.hiz[k] = far_away;
+    dn.child[k] = ~0;
+  }
+  if (lo) {
+    dn.lox[0] = lo[0], dn.hix[0] = hi[0], dn.loy[0] = lo[1], dn.hiy[0] = hi[1], dn.loz[0] = lo[2], dn.hiz[0] = hi[2];
+    dn.child[0] = leaf;
+  }
+  return dn;
+}
+}  // namespace
+
 int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi, FlatScene* out, bool host_bvh) {
   if (world < 0 || (size_t)world >= s.obj.size()) return fail(RTB_ERR_INVALID, "flatten: bad world handle");
   *out = FlatScene();
@@ -387,6 +404,7 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
     dn.n3 = {~0, ~0, 0, 0};
     out->nodes.push_back(dn);
     out->root = 0;
+    out->nodes4.push_back(lone_leaf_node4(nullptr, nullptr, ~0));
     return RTB_OK;
   }
   if (!host_bvh && n >= 2) {
@@ -425,6 +443,7 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
     dn.n3 = {leaf_code(b.nodes[root]), ~0, 0, 0};
     out->nodes.push_back(dn);
     out->root = 0;
+    out->nodes4.push_back(lone_leaf_node4(lo, hi, leaf_code(b.nodes[root])));
     return RTB_OK;
   }
   std::vector<int> dev_index(b.nodes.size(), -1);
@@ -448,6 +467,59 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
     out->nodes[dev_index[i]] = dn;
   }
   out->root = dev_index[root];
+
+  // ---- the same tree, four-wide: a node adopts its grandchildren, largest surface area first, until it has four children
+  // (or only leaves).  Children keep the two-child tree's boxes (already padded the same way), leaves keep their codes.
+  {
+    std::vector<DNode4>& n4 = out->nodes4;
+    n4.clear();
+    const float far_away = 1e30f;  // unused slots: a point no ray meets (and an empty leaf behind it if one ever does)
+    struct Todo { int bn, slot, depth; };
+    std::vector<Todo> todo;  // (BuildNode index, DNode4 index, depth of that node)
+    n4.push_back(DNode4{});
+    todo.push_back({root, 0, 1});
+    int depth4 = 0;
+    while (!todo.empty()) {
+      const int bn_i = todo.back().bn, slot_i = todo.back().slot, depth_i = todo.back().depth;
+      todo.pop_back();
+      depth4 = std::max(depth4, depth_i);
+      const BuildNode& bn = b.nodes[bn_i];
+      std::vector<int> kids = {bn.left, bn.right};
+      while (kids.size() < 4) {
+        int best = -1;
+        double best_area = -1.0;
+        for (size_t k = 0; k < kids.size(); ++k)
+          if (b.nodes[kids[k]].left >= 0 && b.nodes[kids[k]].box.area() > best_area) best_area = b.nodes[kids[k]].box.area(), best = (int)k;
+        if (best < 0) break;
+        const BuildNode& g = b.nodes[kids[best]];
+        kids[best] = g.left;
+        kids.push_back(g.right);
+      }
+      DNode4 dn{};
+      for (int k = 0; k < 4; ++k) {
+        if (k < (int)kids.size()) {
+          const BuildNode& c = b.nodes[kids[k]];
+          float lo[3], hi[3];
+          pad_box(c.box, lo, hi);
+          dn.lox[k] = lo[0], dn.hix[k] = hi[0], dn.loy[k] = lo[1], dn.hiy[k] = hi[1], dn.loz[k] = lo[2], dn.hiz[k] = hi[2];
+          if (c.left >= 0) {
+            dn.child[k] = (int)n4.size();
+            n4.push_back(DNode4{});
+            todo.push_back({kids[k], dn.child[k], depth_i + 1});
+          } else {
+            dn.child[k] = leaf_code(c);
+          }
+        } else {
+          dn.lox[k] = dn.hix[k] = dn.loy[k] = dn.hiy[k] = dn.loz[k] = dn.hiz[k] = far_away;
+          dn.child[k] = ~0;
+        }
+      }
+      n4[slot_i] = dn;
+    }
+    out->root4 = 0;
+    // a step pushes up to three children: the traversal stack (RTB_STACK_DEPTH = 64 entries) must hold 3 per level
+    if (3 * depth4 + 1 > 60) n4.clear();
+  }
   return RTB_OK;
 }
 

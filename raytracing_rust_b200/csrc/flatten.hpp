@@ -10,6 +10,8 @@ namespace rtb {
 
 struct FlatScene {
   std::vector<DNode> nodes;
+  std::vector<DNode4> nodes4;  // the same tree collapsed to four children per node (empty when the device builds the BVH)
+  int root4 = 0;
   std::vector<DPrim> prims;   // BVH leaf order
   std::vector<DPrim> bprims;  // medium boundaries, grouped per medium
   std::vector<DMedium> media;

@@ -95,7 +95,7 @@ __device__ __forceinline__ int tid_here() {
   return t;
 }
 
-template <bool kStats, int kThreads, int kMinBlocks>
+template <bool kStats, int kThreads, int kMinBlocks, bool kWide>
 __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
                                                         unsigned long long* __restrict__ stats,
                                                         unsigned int* __restrict__ work_counter) {
@@ -154,13 +154,33 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
     while (__popc(m_node) >= P.k_node) {
       // ------------------------------------------------------------------ NODE phase
       if (cur >= 0) {
-        if (kStats) cnt.node_tests++;
-        int next, push;
-        const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-        if (nh == 2) *top++ = push;
-        if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
-        cur = next;
+        if (kWide) {  // four child boxes per step (DNode4); counted as two two-box tests
+          if (kStats) cnt.node_tests += 2;
+          cur = node_step4(sv.nodes4, cur, ri, P.t_min, best.t, top);
+        } else {
+          if (kStats) cnt.node_tests++;
+          int next, push;
+          const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+          if (nh == 2) *top++ = push;
+          if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
+          cur = next;
+        }
       }
+#if defined(RTB_NODE_UNROLL) && RTB_NODE_UNROLL == 2  // experiment: two steps per vote (profiles/r2_experiments.txt)
+      if (cur >= 0) {
+        if (kWide) {
+          if (kStats) cnt.node_tests += 2;
+          cur = node_step4(sv.nodes4, cur, ri, P.t_min, best.t, top);
+        } else {
+          if (kStats) cnt.node_tests++;
+          int next, push;
+          const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+          if (nh == 2) *top++ = push;
+          if (nh == 0) next = *--top;
+          cur = next;
+        }
+      }
+#endif
       m_node = __ballot_sync(0xffffffffu, cur >= 0);
     }
     // waiting lanes can only be released (and new ones only appear) after a SHADE round: test then, not every round
@@ -307,18 +327,23 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
           top = stack + 1;
-          cur = sv.root;
+          cur = kWide ? sv.root4 : sv.root;
         }
       }
       check_wait = true;
     } else if (phase == 0) {
       if (cur >= 0) {  // below-threshold NODE step
-        if (kStats) cnt.node_tests++;
-        int next, push;
-        const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-        if (nh == 2) *top++ = push;
-        if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
-        cur = next;
+        if (kWide) {
+          if (kStats) cnt.node_tests += 2;
+          cur = node_step4(sv.nodes4, cur, ri, P.t_min, best.t, top);
+        } else {
+          if (kStats) cnt.node_tests++;
+          int next, push;
+          const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+          if (nh == 2) *top++ = push;
+          if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
+          cur = next;
+        }
       }
     } else {
       // ------------------------------------------------------------------ LEAF phase
@@ -482,6 +507,11 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   } else if ((rc = upload_vec(d, f.nodes, &v.nodes)) || (rc = upload_vec(d, f.prims, &v.prims))) {
     return rc;
   }
+  v.nodes4 = nullptr, v.root4 = 0;
+  if (!device_bvh && !f.nodes4.empty()) {
+    if ((rc = upload_vec(d, f.nodes4, &v.nodes4))) return rc;
+    v.root4 = f.root4;
+  }
   if ((rc = upload_vec(d, f.bprims, &v.bprims)) || (rc = upload_vec(d, f.media, &v.media)) ||
       (rc = upload_vec(d, f.xforms, &v.xforms)) || (rc = upload_vec(d, f.mats, &v.mats)) ||
       (rc = upload_vec(d, f.texs, &v.texs)) || (rc = upload_vec(d, f.perlin, &v.perlin)) ||
@@ -604,21 +634,31 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     // 228 KB array stays L1 — the BVH (90 KB) and primitives (68 KB) live there and throughput follows the L1 size
     // (carveout 100 %: -21 %, profiles/r1_experiments.txt).  o.reserved[5] overrides for experiments.
     const int carveout = o.reserved[5] > 0 ? o.reserved[5] : std::min(100, (min_blocks * (14 * 1024 + 1024) * 100) / (228 * 1024) + 5);
-#define RTB_LAUNCH_MEGA(ST, TH, MB)                                                                                   \
+#define RTB_LAUNCH_MEGA(ST, TH, MB, WD)                                                                               \
   do {                                                                                                                \
-    cudaFuncSetAttribute(k_render_mega<ST, TH, MB>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);        \
-    k_render_mega<ST, TH, MB><<<(unsigned)blocks, TH, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);           \
+    cudaFuncSetAttribute(k_render_mega<ST, TH, MB, WD>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);    \
+    k_render_mega<ST, TH, MB, WD><<<(unsigned)blocks, TH, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);       \
   } while (0)
+    // which tree: the four-wide one when flatten built it (host SAH builder) unless opts.reserved[6] == 2 asks for the
+    // two-child tree (A/B runs); the 128-thread occupancy points exist for the two-child tree only
+    const bool wide = d->view.nodes4 != nullptr && o.reserved[6] != 2 && block == 256;
     if (o.collect_stats) {
-      if (block == 256) RTB_LAUNCH_MEGA(true, 256, 2); else RTB_LAUNCH_MEGA(true, 128, 4);
+      if (block == 256) { if (wide) RTB_LAUNCH_MEGA(true, 256, 2, true); else RTB_LAUNCH_MEGA(true, 256, 2, false); }
+      else RTB_LAUNCH_MEGA(true, 128, 4, false);
+    } else if (wide) {
+      switch (min_blocks) {
+        case 2: RTB_LAUNCH_MEGA(false, 256, 2, true); break;
+        case 4: RTB_LAUNCH_MEGA(false, 256, 4, true); break;
+        default: RTB_LAUNCH_MEGA(false, 256, 3, true); break;
+      }
     } else {
       switch (min_blocks) {
-        case 2: RTB_LAUNCH_MEGA(false, 256, 2); break;
-        case 4: RTB_LAUNCH_MEGA(false, 256, 4); break;
-        case 5: RTB_LAUNCH_MEGA(false, 128, 5); break;
-        case 6: RTB_LAUNCH_MEGA(false, 128, 6); break;
-        case 7: RTB_LAUNCH_MEGA(false, 128, 7); break;
-        default: RTB_LAUNCH_MEGA(false, 256, 3); break;
+        case 2: RTB_LAUNCH_MEGA(false, 256, 2, false); break;
+        case 4: RTB_LAUNCH_MEGA(false, 256, 4, false); break;
+        case 5: RTB_LAUNCH_MEGA(false, 128, 5, false); break;
+        case 6: RTB_LAUNCH_MEGA(false, 128, 6, false); break;
+        case 7: RTB_LAUNCH_MEGA(false, 128, 7, false); break;
+        default: RTB_LAUNCH_MEGA(false, 256, 3, false); break;
       }
     }
     ++*launches;

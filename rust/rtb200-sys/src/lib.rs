@@ -48,8 +48,14 @@ pub struct rtb_render_opts {
     pub pipeline: c_int,
     pub device: c_int,
     pub collect_stats: c_int,
+    pub band_begin: c_int,  // row-band sharding: 4-row bands band_begin + i*band_stride (tests/test.rs:62-63 split)
+    pub band_stride: c_int,
+    pub multi_shard: c_int, // rtb_render_multi: RTB_SHARD_SAMPLES | RTB_SHARD_BANDS
     pub reserved: [c_int; 7],
 }
+pub const RTB_SHARD_SAMPLES: c_int = 0;
+pub const RTB_SHARD_BANDS: c_int = 1;
+pub const RTB_BAND_ROWS: c_int = 4;
 
 #[repr(C)]
 #[derive(Clone, Copy, Debug, Default)]
@@ -133,4 +139,29 @@ extern "C" {
     pub fn rtb_peer_open(handle64: *const u8, device: c_int, d_ptr: *mut *mut c_void) -> c_int;
     pub fn rtb_peer_close(d_ptr: *mut c_void) -> c_int;
     pub fn rtb_reduce_resolve_device(d_sums: *const *const f32, n_bufs: c_int, nx: c_int, ny: c_int, ns: c_int, d_total: *mut f32, d_rgb8: *mut u8, stream: *mut c_void) -> c_int;
+    pub fn rtb_reduce_resolve_range_device(d_sums: *const *const f32, n_bufs: c_int, first_value: usize, n_values: usize, ns: c_int, d_total: *mut f32,
+                                           d_rgb8: *mut u8, stream: *mut c_void) -> c_int;
+    pub fn rtb_resolve_bands_device(d_sum_rgb: *const f32, nx: c_int, ny: c_int, ns: c_int, band_begin: c_int, band_stride: c_int, d_rgb8: *mut u8,
+                                    compact: c_int, stream: *mut c_void) -> c_int;
+    pub fn rtb_resolve_device(d_sum_rgb: *const f32, nx: c_int, ny: c_int, ns: c_int, d_rgb8: *mut u8, stream: *mut c_void) -> c_int;
+    pub fn rtb_scene_device_bytes(s: *const rtb_scene) -> usize;
+    // scene bytes (.rtscene, include/rtb_scene_format.h) and the named scene constructors of tests/test.rs:89-523
+    pub fn rtb_scene_serialized_size(s: *const rtb_scene) -> usize;
+    pub fn rtb_scene_serialize(s: *const rtb_scene, buf: *mut c_void, cap: usize) -> c_int;
+    pub fn rtb_scene_deserialize(buf: *const c_void, len: usize) -> *mut rtb_scene;
+    pub fn rtb_scene_prim_count(s: *mut rtb_scene, world: c_int) -> c_int;
+    pub fn rtb_scene_named(s: *mut rtb_scene, name: *const c_char, seed: u64, earth_rgb8: *const u8, earth_nx: u32, earth_ny: u32, nx: c_int, ny: c_int,
+                           camera: *mut RtbCamera) -> c_int;
+    // parity hooks: Hittable::hit(ray, t_min, MAX) (src/color.rs:7) and single stages of the device path (csrc/debug.cu)
+    pub fn rtb_closest_hit(s: *mut rtb_scene, world: c_int, rays: *const f64, n: usize, t_min: c_double, device: c_int, out_prim: *mut i32, out_t: *mut f32) -> c_int;
+    pub fn rtb_closest_hit_ex(s: *mut rtb_scene, world: c_int, rays: *const f64, n: usize, t_min: c_double, self_id: *const i32, device: c_int,
+                              out_prim: *mut i32, out_rec: *mut f32) -> c_int;
+    pub fn rtb_primary_rays(cam: *const RtbCamera, nx: c_int, ny: c_int, s: c_int, seed: u64, out_rays: *mut f64) -> c_int;
+    pub fn rtb_debug_camera_rays(cam: *const RtbCamera, nx: c_int, ny: c_int, s: c_int, seed: u64, device: c_int, out_rays: *mut f32) -> c_int;
+    pub fn rtb_debug_camera_draws(nx: c_int, ny: c_int, s: c_int, seed: u64, out: *mut f64) -> c_int;
+    pub fn rtb_debug_scatter(s: *mut rtb_scene, world: c_int, mat: c_int, input: *const f64, n: usize, seed: u64, device: c_int, out: *mut f32) -> c_int;
+    pub fn rtb_debug_sample(kind: c_int, seed: u64, n: usize, device: c_int, out: *mut f32) -> c_int;
+    pub fn rtb_debug_texture_value(s: *mut rtb_scene, world: c_int, tex: c_int, uvp: *const f64, n: usize, device: c_int, out: *mut f32) -> c_int;
+    pub fn rtb_philox4x32_10(counter: *const u32, key: *const u32, out: *mut u32) -> c_int;
+    pub fn rtb_issue_peak(device: c_int, fma_tlane_per_s: *mut f64, mixed_tlane_per_s: *mut f64, slab_tlane_per_s: *mut f64) -> c_int;
 }

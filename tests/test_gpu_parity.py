@@ -243,6 +243,26 @@ def test_wavefront_equals_megakernel(rtb, name, bg):
     _assert_same_estimate(a, b)
 
 
+@pytest.mark.parametrize("name,bg,nx,ny", [("cornell_box", 0, 96, 64), ("final_scene_lit", 0, 160, 90), ("random_scene", 1, 93, 61),
+                                           ("cornell_smoke_book", 0, 64, 64), ("earth", 1, 37, 19), ("two_spheres", 1, 64, 36)])
+def test_four_wide_tree_traces_the_same_paths_as_the_two_child_tree(rtb, name, bg, nx, ny):
+    # closest hits do not depend on the tree: with the same counter-based draws every path is the same path, so the segment,
+    # primitive-test-free counters (shade, texture) and the image agree; only node / primitive test counts may differ
+    ns = 16
+    s, w, cam = rtb.Scene.named(name, nx, ny)
+    o4 = rtb.default_opts(background=bg, seed=4, collect_stats=1)
+    o2 = rtb.default_opts(background=bg, seed=4, collect_stats=1)
+    o2.reserved[6] = 2
+    a, _, sa = s.render(w, cam, nx, ny, ns, o4, want_rgb8=False, want_stats=True)
+    b, _, sb = s.render(w, cam, nx, ny, ns, o2, want_rgb8=False, want_stats=True)
+    for k in ("paths", "segments", "shade", "tex_evals", "medium_tests"):
+        assert sa[k] == sb[k], (k, sa[k], sb[k])
+    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)
+    assert sa["node_tests"] != sb["node_tests"]  # it really was the other tree
+    print(name, "node tests (2-box units) per segment: 4-wide", sa["node_tests"] / sa["segments"], "2-wide", sb["node_tests"] / sb["segments"],
+          "prim tests per segment", sa["prim_tests"] / sa["segments"], sb["prim_tests"] / sb["segments"])
+
+
 def test_wavefront_small_capacity_and_sharding(rtb):
     # more paths than slots (pool recycling) and a sample shard, against the megakernel
     nx, ny, ns = 64, 48, 20
@@ -281,8 +301,9 @@ def test_pool_sample_sharding_and_stats(rtb):
     whole, _, st = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=9, pipeline=rtb.PIPE_POOL, collect_stats=1), want_rgb8=False,
                             want_stats=True)
     np.testing.assert_allclose(parts[0] + parts[1] + parts[2], whole, rtol=1e-4, atol=1e-4)
-    ref, _, sr = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=9, pipeline=rtb.PIPE_MEGAKERNEL, collect_stats=1), want_rgb8=False,
-                          want_stats=True)
+    o_ref = rtb.default_opts(seed=9, pipeline=rtb.PIPE_MEGAKERNEL, collect_stats=1)
+    o_ref.reserved[6] = 2  # the two-child tree, the one the pool traverses (the megakernel's default is the four-wide tree)
+    ref, _, sr = s.render(w, cam, nx, ny, ns, o_ref, want_rgb8=False, want_stats=True)
     assert st["node_tests"] == sr["node_tests"] and st["prim_tests"] == sr["prim_tests"] and st["shade"] == sr["shade"]
 
 
@@ -293,7 +314,9 @@ def test_dual_equals_megakernel(rtb, name, bg, nx, ny):
     ns = 24
     s, w, cam = rtb.Scene.named(name, nx, ny)
     kw = dict(background=bg, seed=4, collect_stats=1, sample_begin=1, sample_stride=2)
-    a, _, sa = s.render(w, cam, nx, ny, ns, rtb.default_opts(pipeline=rtb.PIPE_MEGAKERNEL, **kw), want_rgb8=False, want_stats=True)
+    o_ref = rtb.default_opts(pipeline=rtb.PIPE_MEGAKERNEL, **kw)
+    o_ref.reserved[6] = 2  # the two-child tree, the one this pipeline traverses
+    a, _, sa = s.render(w, cam, nx, ny, ns, o_ref, want_rgb8=False, want_stats=True)
     b, _, sb = s.render(w, cam, nx, ny, ns, rtb.default_opts(pipeline=rtb.PIPE_DUAL, **kw), want_rgb8=False, want_stats=True)
     assert sb["paths"] == nx * ny * (ns // 2)
     for k in ("segments", "node_tests", "prim_tests", "shade"):

@@ -32,6 +32,7 @@ static void make_view(EmuScene* e) {
   v.xforms = f.xforms.data(), v.mats = f.mats.data(), v.texs = f.texs.data(), v.perlin = f.perlin.data();
   v.texels = f.texels.data();
   v.n_nodes = (int)f.nodes.size(), v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size(), v.root = f.root;
+  v.nodes4 = f.nodes4.empty() ? nullptr : f.nodes4.data(), v.root4 = f.root4;
   e->id_table.assign(std::max(1, f.n_prim_ids), 0);
   for (int p = 0; p < v.n_prims; ++p) {
     const int n = RTB_PRIM_TYPE(f.prims[p].c.x) == DP_BOX ? 6 : 1;
@@ -53,6 +54,11 @@ void* emu_scene_load(const void* bytes, size_t len, int world) {
   }
   make_view(e);
   return e;
+}
+// width 2: the two-child tree; 4: the four-wide tree (default when flatten built it)
+void emu_set_bvh_width(void* p, int width) {
+  EmuScene* e = (EmuScene*)p;
+  e->view.nodes4 = (width == 4 && !e->flat.nodes4.empty()) ? e->flat.nodes4.data() : nullptr;
 }
 void emu_scene_free(void* p) {
   EmuScene* e = (EmuScene*)p;

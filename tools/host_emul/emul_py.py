@@ -24,6 +24,7 @@ _vp, _i, _d, _u64, _sz = C.c_void_p, C.c_int, C.c_double, C.c_uint64, C.c_size_t
 lib.emu_scene_load.restype = _vp
 lib.emu_scene_load.argtypes = [_vp, _sz, _i]
 lib.emu_scene_free.argtypes = [_vp]
+lib.emu_set_bvh_width.argtypes = [_vp, _i]
 lib.emu_closest_hit_ex.argtypes = [_vp, _vp, _sz, _d, _vp, _vp, _vp, _vp]
 lib.emu_scatter.argtypes = [_vp, _i, _vp, _sz, _u64, _vp]
 lib.emu_sample.argtypes = [_i, _u64, _sz, _vp]
@@ -46,6 +47,9 @@ class EmuScene:
         p, self._p = getattr(self, "_p", None), None
         if p:
             lib.emu_scene_free(p)
+
+    def set_bvh_width(self, width):
+        lib.emu_set_bvh_width(self._p, width)
 
     def closest_hit_ex(self, world, rays, self_id=None, t_min=1e-3, device=0, want_rec=True):
         r = np.ascontiguousarray(rays, dtype=np.float64)
