@@ -11,7 +11,7 @@ GENCODE := -gencode arch=compute_100a,code=sm_100a
 NVCCFLAGS := -O3 -std=c++17 $(GENCODE) -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unknown-pragmas -Iinclude -I$(CSRC) \
              -Xptxas -v --expt-relaxed-constexpr $(EXTRA) $(NVEXTRA)
 HOST_SRCS := $(CSRC)/scene.cpp $(CSRC)/scenes_named.cpp $(CSRC)/flatten.cpp $(CSRC)/image_io.cpp
-CU_SRCS := $(CSRC)/render.cu $(CSRC)/wavefront.cu $(CSRC)/peer.cu $(CSRC)/pool.cu $(CSRC)/dual.cu $(CSRC)/multi.cu $(CSRC)/calib.cu $(CSRC)/bvh_build.cu $(CSRC)/debug.cu
+CU_SRCS := $(CSRC)/render.cu $(CSRC)/wavefront.cu $(CSRC)/peer.cu $(CSRC)/multi.cu $(CSRC)/calib.cu $(CSRC)/bvh_build.cu $(CSRC)/debug.cu
 HDRS := $(wildcard include/*.h include/*.hpp $(CSRC)/*.h $(CSRC)/*.hpp $(CSRC)/*.cuh)
 OBJS := $(patsubst $(CSRC)/%.cpp,$(B)/%.o,$(HOST_SRCS)) $(patsubst $(CSRC)/%.cu,$(B)/%.cu.o,$(CU_SRCS))
 

@@ -133,9 +133,12 @@ def run_configs_table(args):
 
     configs = [("C1", "two_spheres", 400, 225, 100), ("C2", "random_scene", 1920, 1080, 500), ("C3", "two_perlin_sphere", 1920, 1080, 1000),
                ("C3", "earth", 1920, 1080, 1000), ("C4", "cornell_box", 1024, 1024, 10000), ("C4", "cornell_smoke", 1024, 1024, 10000),
-               ("C5", "final_scene", 3840, 2160, 10000)]
+               ("C5", "final_scene", 3840, 2160, 10000),
+               # the lit variant of C5 (light rect bounds ordered): radiance is non-zero, so the accumulation path (shared-memory
+               # atomics, RED.global flush) is live in the timed launch — the as-written scene is black (F4) and never adds
+               ("C5-lit", "final_scene_lit", 3840, 2160, 1000)]
     nth = os.cpu_count() or 1
-    print(f"| cfg | scene (as written, black background) | image | spp | paths | GPU s | GPU Mpaths/s | GPU Mseg/s | seg/path | "
+    print(f"| cfg | scene (as written, black background; C5-lit = labelled lit variant) | image | spp | paths | GPU s | GPU Mpaths/s | GPU Mseg/s | seg/path | "
           f"CPU oracle Mpaths/s ({nth} thr) | CPU sample | speed-up |")
     print("|---|---|---|---:|---:|---:|---:|---:|---:|---:|---|---:|")
     for cfg, name, nx, ny, ns in configs:

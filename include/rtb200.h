@@ -44,8 +44,8 @@ enum RtbPipeline {
   RTB_PIPE_AUTO = 0,
   RTB_PIPE_MEGAKERNEL = 1, /* one persistent kernel, path regeneration */
   RTB_PIPE_WAVEFRONT = 2,  /* raygen / extend / per-material shade queues, path state in HBM */
-  RTB_PIPE_POOL = 3,       /* per-SM path pool in shared memory, warps regroup paths by phase */
-  RTB_PIPE_DUAL = 4        /* the megakernel's scheduler with two paths per lane (state in shared memory) */
+  RTB_PIPE_POOL = 3,       /* removed (round-1 experiment: per-SM path pool in shared memory; slower, profiles/r1_pool.txt) */
+  RTB_PIPE_DUAL = 4        /* removed (round-1 experiment: two paths per lane; slower, profiles/r1_dual.txt) */
 };
 
 const char* rtb_last_error(void);
@@ -90,7 +90,15 @@ int rtb_obj_constant_medium(rtb_scene*, int boundary, double density, int tex); 
 int rtb_obj_list(rtb_scene*, const int* objs, int n);         /* HittableList push order, src/hittable.rs:23-34 */
 /* BVHNode::new(&mut [Rc<dyn Hittable>], time0, time1), src/bvh.rs:17.  Fails with
  * RTB_ERR_NO_BBOX if n == 0.  `seed` drives the oracle's split-axis stream; the GPU builds its
- * own SAH tree over the same primitives (closest-hit results do not depend on the tree). */
+ * own SAH tree over the TRUE bounds of the same primitives, so a BVHNode answers exactly like the
+ * HittableList of the same children.  That equals the reference wherever the reference's bounding
+ * boxes are right — every shipped scene — and differs, deliberately, in two corners where upstream
+ * bounding-box bugs leak into its results:
+ *   * Rect::bounding_box ignores `plane` (src/rect.rs:71-75, Q8): a ZX / YZ Rect placed DIRECTLY in
+ *     a BVHNode is culled upstream by a box in the wrong plane; here it is hit (XY Rects and Cubes,
+ *     which override the box, agree).  tests/test_gpu_fields.py pins this.
+ *   * a one-element BVHNode stores its child in both slots (src/bvh.rs:43-45): a ConstantMedium
+ *     there draws two free-flight distances upstream and keeps the nearer; here it draws one. */
 int rtb_obj_bvh(rtb_scene*, const int* objs, int n, double time0, double time1, uint64_t seed);
 
 /* ---- named scenes: tests/test.rs:89-523 ---------------------------------------------------
@@ -284,6 +292,12 @@ int rtb_debug_scatter(rtb_scene*, int world, int mat, const double* in, size_t n
 /* The device samplers that replace the rejection loops of src/util.rs:4-24: kind 0 = uniform in the unit ball (scatter),
  * kind 1 = uniform in the unit disk (lens).  out = n x {x, y, z} floats. */
 int rtb_debug_sample(int kind, uint64_t seed, size_t n, int device, float* out);
+
+/* Self-checking builds (make NVEXTRA=-DRTB_DEBUG_CHECKS=1): every index the kernels form (traversal stack, node /
+ * primitive / material / texture / texel, shared tiles, output pixels, wavefront queues) is bounds-checked on the device and
+ * violations are counted per class; this reads and clears the 16 counters (all zero = clean).  The stand-in for
+ * compute-sanitizer, which the GPU pool does not offer.  Release builds: RTB_ERR_INVALID. */
+int rtb_debug_check_failures(int device, uint32_t out[16]);
 
 /* P3 text exactly as tests/test.rs:59,79: "P3\n{nx} {ny}\n255\n" + "{r} {g} {b}\n" per pixel.
  * Returns the byte count (excluding NUL); writes at most cap bytes. */

@@ -146,6 +146,7 @@ _sig("rtb_debug_camera_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _i, _v
 _sig("rtb_debug_camera_draws", _i, _i, _i, _i, _u64, _vp)
 _sig("rtb_debug_scatter", _i, _vp, _i, _i, _vp, _sz, _u64, _i, _vp)
 _sig("rtb_debug_sample", _i, _i, _u64, _sz, _i, _vp)
+_sig("rtb_debug_check_failures", _i, _i, C.POINTER(C.c_uint32))
 _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
 _sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
 _sig("rtb_ppm_p6", _sz, _vp, _i, _i, _vp, _sz)
@@ -538,6 +539,14 @@ def camera_draws(nx, ny, sample=0, seed=1) -> np.ndarray:
     out = np.empty((nx * ny, 5), np.float64)
     _h(lib.rtb_debug_camera_draws(nx, ny, sample, seed, out.ctypes.data), "debug_camera_draws")
     return out
+
+
+def check_failures(device=0):
+    """Self-check counters of an RTB_DEBUG_CHECKS build (read and cleared); raises RtbError on a release build."""
+    out = (C.c_uint32 * 16)()
+    _h(lib.rtb_debug_check_failures(device, out), "debug_check_failures")
+    names = ["stack", "node", "prim", "mat", "tex", "texel", "tile", "pixel", "queue", "nan"]
+    return {n: int(out[i]) for i, n in enumerate(names)}
 
 
 def device_sample(kind, seed, n, device=0) -> np.ndarray:

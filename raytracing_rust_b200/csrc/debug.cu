@@ -21,6 +21,9 @@
 
 namespace rtb {
 
+RTB_DEFINE_CHECK_READER(read_checks_debug)
+
+
 #define CUDA_TRY(expr)                                                                                              \
   do {                                                                                                              \
     cudaError_t e_ = (expr);                                                                                        \
@@ -170,7 +173,7 @@ int rtb_closest_hit_ex(rtb_scene* s, int world, const double* rays, size_t n, do
     if (d->view.n_prims > 0)
       k_id_table<<<(d->view.n_prims + 255) / 256, 256>>>(d->view.prims, d->view.n_prims, d_table.as<int>(), n_ids);
   }
-  k_closest_hit_ex<<<(unsigned)((n + 255) / 256), 256>>>(d->view, d_rays.as<float>(), n, (float)t_min, d_self.as<int>(),
+  k_closest_hit_ex<<<(unsigned)((n + 255) / 256), 256>>>(view_with_width(d, 0), d_rays.as<float>(), n, (float)t_min, d_self.as<int>(),
                                                          d_table.as<int>(), d_prim.as<int>(), d_rec.as<float>());
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaMemcpy(out_prim, d_prim.p, n * sizeof(int), cudaMemcpyDeviceToHost));

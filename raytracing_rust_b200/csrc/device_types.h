@@ -112,6 +112,7 @@ struct SceneView {
   const uint32_t* texels;  // RGBA8
   int n_nodes, n_prims, n_media, root;  // root: node index (always an inner node)
   int root4;                            // root of nodes4
+  int n_nodes4, n_mats, n_texs, n_texels;  // table sizes (the RTB_DEBUG_CHECKS build compares every index with them)
 };
 
 struct DCamera {  // src/camera.rs:8-18, f32

@@ -181,6 +181,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
         }
       }
 #endif
+      RTB_CHECK(top >= stack && top <= stack + RTB_STACK_DEPTH, RTB_CHK_STACK);
+      RTB_CHECK(cur < (kWide ? sv.n_nodes4 : sv.n_nodes), RTB_CHK_NODE);
       m_node = __ballot_sync(0xffffffffu, cur >= 0);
     }
     // waiting lanes can only be released (and new ones only appear) after a SHADE round: test then, not every round
@@ -259,6 +261,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
               s.n = mk(1.f, 0.f, 0.f);
               s.u = 0.f, s.v = 0.f;
               s.mat = P.n_const_media >= 0 ? (medium == 0 ? P.cmedia_mat[0] : P.cmedia_mat[1]) : __ldg(&sv.media[medium].mat);
+              RTB_CHECK(s.mat >= 0 && s.mat < sv.n_mats, RTB_CHK_MAT);
               m = __ldg(reinterpret_cast<const int4*>(sv.mats + s.mat));
               self_prim = -1;
             } else {
@@ -285,6 +288,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             rad = thr * background_color(P.background, ray.d);  // miss, src/color.rs:17-22
           }
           if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
+            RTB_CHECK(pix_local >= 0 && pix_local < 64 && wib >= 0 && wib < 8, RTB_CHK_TILE);
+            RTB_CHECK(rad.x == rad.x && rad.y == rad.y && rad.z == rad.z, RTB_CHK_NAN);
             float* a = &s_acc[wib][pix_local >> 5][(pix_local & 31) * 3];
             atomicAdd(a, rad.x);
             atomicAdd(a + 1, rad.y);
@@ -313,6 +318,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             sample = (uint32_t)(P.sample_first + k * P.sample_step);
             const int i = info.x + lx, row = info.y + ly;  // row 0 = top of the image = j = ny-1 (tests/test.rs:62)
             pixel = (uint32_t)(row * P.nx + i);
+            RTB_CHECK(i >= 0 && i < P.nx && row >= 0 && row < P.ny && pl >= 0 && pl < 32, RTB_CHK_PIXEL);
             ray = camera_ray(cam, i, P.ny - 1 - row, P.nx, P.ny, P.keys, pixel, sample);
             thr = mk(1.f, 1.f, 1.f);
             depth = 0, self_prim = -1, self_face = 0;
@@ -350,6 +356,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
       if (cur < 0 && cur > CUR_DONE) {
         const unsigned code = ~(unsigned)cur;
         const int first = (int)(code >> 3), count = (int)(code & 7u);
+        RTB_CHECK(first >= 0 && first + count <= sv.n_prims, RTB_CHK_PRIM);
+        RTB_CHECK(top > stack && top <= stack + RTB_STACK_DEPTH, RTB_CHK_STACK);
         for (int q = 0; q < count; ++q) {
           const int pi = first + q;
           float t;
@@ -447,6 +455,17 @@ struct StageTimer {
   }
 };
 
+RTB_DEFINE_CHECK_READER(read_checks_render)
+
+SceneView view_with_width(const DeviceScene* d, int width) {
+  SceneView v = d->view;
+  if (width == 0)
+    if (const char* e = std::getenv("RTB200_BVH_WIDTH")) width = std::atoi(e);
+  if (width == 2) v.nodes4 = nullptr;
+  else if (width == 4 && d->d_nodes4) v.nodes4 = d->d_nodes4;
+  return v;
+}
+
 void destroy_device_scene(DeviceScene* d) {
   if (!d) return;
   int prev = 0;
@@ -509,8 +528,13 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   }
   v.nodes4 = nullptr, v.root4 = 0;
   if (!device_bvh && !f.nodes4.empty()) {
-    if ((rc = upload_vec(d, f.nodes4, &v.nodes4))) return rc;
+    if ((rc = upload_vec(d, f.nodes4, &d->d_nodes4))) return rc;
     v.root4 = f.root4;
+    // Which tree the kernels walk by default, by measurement (profiles/r2_experiments.txt): the four-wide tree wins on
+    // small media-free scenes (cornell_box +5.8 %, simple_light +5.7 %: half the steps, and the whole tree is 1-3 nodes),
+    // the two-child tree everywhere else (final_scene -6..9 %: same box tests, a 2x longer loop body, more spills).
+    const size_t np = f.prims.size();
+    if (np >= 3 && np <= 64 && f.media.empty()) v.nodes4 = d->d_nodes4;
   }
   if ((rc = upload_vec(d, f.bprims, &v.bprims)) || (rc = upload_vec(d, f.media, &v.media)) ||
       (rc = upload_vec(d, f.xforms, &v.xforms)) || (rc = upload_vec(d, f.mats, &v.mats)) ||
@@ -521,6 +545,7 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   tm.lap("table uploads");
   if (!device_bvh) v.n_nodes = (int)f.nodes.size(), d->n_nodes_device = v.n_nodes;
   v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
+  v.n_nodes4 = (int)f.nodes4.size(), v.n_mats = (int)f.mats.size(), v.n_texs = (int)f.texs.size(), v.n_texels = (int)f.texels.size();
   v.root = f.root;
   void* st = nullptr;
   CUDA_TRY(cudaMalloc(&st, 32 * sizeof(unsigned long long)));
@@ -637,11 +662,12 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
 #define RTB_LAUNCH_MEGA(ST, TH, MB, WD)                                                                               \
   do {                                                                                                                \
     cudaFuncSetAttribute(k_render_mega<ST, TH, MB, WD>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);    \
-    k_render_mega<ST, TH, MB, WD><<<(unsigned)blocks, TH, 0, stream>>>(d->view, cam, P, d_sum, d->d_stats, wc);       \
+    k_render_mega<ST, TH, MB, WD><<<(unsigned)blocks, TH, 0, stream>>>(view, cam, P, d_sum, d->d_stats, wc);          \
   } while (0)
-    // which tree: the four-wide one when flatten built it (host SAH builder) unless opts.reserved[6] == 2 asks for the
-    // two-child tree (A/B runs); the 128-thread occupancy points exist for the two-child tree only
-    const bool wide = d->view.nodes4 != nullptr && o.reserved[6] != 2 && block == 256;
+    // which tree: the upload-time choice (ensure_uploaded) unless opts.reserved[6] = 2 / 4 forces the two-child / four-wide
+    // one (A/B runs); the 128-thread occupancy points exist for the two-child tree only
+    const SceneView view = view_with_width(d, o.reserved[6]);
+    const bool wide = view.nodes4 != nullptr && block == 256;
     if (o.collect_stats) {
       if (block == 256) { if (wide) RTB_LAUNCH_MEGA(true, 256, 2, true); else RTB_LAUNCH_MEGA(true, 256, 2, false); }
       else RTB_LAUNCH_MEGA(true, 128, 4, false);
@@ -693,6 +719,23 @@ void rtb_render_opts_default(rtb_render_opts* o) {
   o->pipeline = RTB_PIPE_AUTO;
 }
 
+// RTB_DEBUG_CHECKS builds: the per-class violation counters of the kernels' self-checks (trace.cuh RtbCheck), read and
+// cleared.  Release builds have no checks compiled in and return RTB_ERR_INVALID.
+int rtb_debug_check_failures(int device, uint32_t out[16]) {
+#if defined(RTB_DEBUG_CHECKS)
+  if (!out) return fail(RTB_ERR_INVALID, "debug_check_failures: null argument");
+  CUDA_TRY(cudaSetDevice(device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  unsigned int h[16] = {0};
+  if (read_checks_render(h) || read_checks_wavefront(h) || read_checks_debug(h)) return fail(RTB_ERR_CUDA, "debug_check_failures: counter read failed");
+  for (int i = 0; i < 16; ++i) out[i] = h[i];
+  return RTB_OK;
+#else
+  (void)device, (void)out;
+  return fail(RTB_ERR_INVALID, "debug_check_failures: this build has no self-checks (compile with -DRTB_DEBUG_CHECKS=1)");
+#endif
+}
+
 int rtb_scene_upload(rtb_scene* s, int world, int device) { return ensure_uploaded(s, world, device, 0.0, 1.0); }
 
 size_t rtb_scene_device_bytes(const rtb_scene* s) {
@@ -737,13 +780,11 @@ int rtb_render_device(rtb_scene* s, const RtbCamera* camera, int nx, int ny, int
     return fail(RTB_ERR_INVALID, "render_device: row-band sharding is implemented by the megakernel pipeline only");
   if (opts->band_begin < 0 || opts->band_stride < 0 || (opts->band_stride <= 1 && opts->band_begin > 0))
     return fail(RTB_ERR_INVALID, "render_device: bad band_begin / band_stride");
-  if (pipe == RTB_PIPE_POOL && !pool_supports(d)) pipe = RTB_PIPE_MEGAKERNEL;  // BVH deeper than the pool's stack
+  if (pipe == RTB_PIPE_POOL || pipe == RTB_PIPE_DUAL)
+    return fail(RTB_ERR_INVALID, "render_device: RTB_PIPE_POOL / RTB_PIPE_DUAL were experiments of round 1 (slower than the megakernel, "
+                                 "profiles/r1_pool.txt, r1_dual.txt) and have been removed");
   if (pipe == RTB_PIPE_WAVEFRONT)
     rc = launch_wavefront(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
-  else if (pipe == RTB_PIPE_POOL)
-    rc = launch_pool(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
-  else if (pipe == RTB_PIPE_DUAL)
-    rc = launch_dual(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
   else
     rc = launch_mega(d, cam, nx, ny, ns, *opts, d_sum_rgb, stream, &launches);
   if (rc != RTB_OK) return rc;
@@ -1021,7 +1062,7 @@ int rtb_closest_hit(rtb_scene* s, int world, const double* rays, size_t n, doubl
   CUDA_TRY(cudaMalloc(&d_t, n * sizeof(float)));
   CUDA_TRY(cudaMalloc(&d_prim, n * sizeof(int)));
   CUDA_TRY(cudaMemcpy(d_rays, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
-  k_closest_hit<<<(unsigned)((n + 255) / 256), 256>>>(s->dev->view, d_rays, n, (float)t_min, d_prim, d_t);
+  k_closest_hit<<<(unsigned)((n + 255) / 256), 256>>>(view_with_width(s->dev, 0), d_rays, n, (float)t_min, d_prim, d_t);
   CUDA_TRY(cudaGetLastError());
   CUDA_TRY(cudaMemcpy(out_prim, d_prim, n * sizeof(int), cudaMemcpyDeviceToHost));
   if (out_t) CUDA_TRY(cudaMemcpy(out_t, d_t, n * sizeof(float), cudaMemcpyDeviceToHost));

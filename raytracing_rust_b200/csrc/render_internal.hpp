@@ -23,29 +23,23 @@ struct DeviceScene {
   cudaDeviceProp prop{};
   WavefrontState* wf = nullptr;
   int n_nodes_device = 0;  // BVH nodes resident on the device (host- or device-built)
+  const DNode4* d_nodes4 = nullptr;  // the four-wide form of the tree (host builder only); view.nodes4 = this or nullptr
 };
+
+// The scene tables as a kernel should see them: width 0 = the upload-time choice of tree (d->view), 2 = the two-child
+// tree, 4 = the four-wide tree when it exists.  RTB200_BVH_WIDTH=2|4 in the environment overrides width 0 (experiments).
+SceneView view_with_width(const DeviceScene* d, int width);
 
 // bvh_build.cu: LBVH over d->flat.prims on the device; sets view.nodes / view.prims / flat.root / flat.bvh_depth
 int build_bvh_device(DeviceScene* d);
 
+// per-translation-unit readers of the RTB_DEBUG_CHECKS counters (trace.cuh RTB_DEFINE_CHECK_READER): add into acc[16], clear
+int read_checks_render(unsigned int* acc);
+int read_checks_wavefront(unsigned int* acc);
+int read_checks_debug(unsigned int* acc);
+
 int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi);
 void make_device_camera(const RtbCamera& c, DCamera* out);
-// pool.cu: path pool in shared memory (RTB_PIPE_POOL); needs bvh depth < RTB_POOL_STACK
-#ifndef RTB_POOL_ROWS
-#define RTB_POOL_ROWS 32
-#endif
-#ifndef RTB_POOL_THREADS
-#define RTB_POOL_THREADS 768
-#endif
-#ifndef RTB_POOL_STACK
-#define RTB_POOL_STACK 16
-#endif
-bool pool_supports(const DeviceScene* d);
-int launch_pool(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
-                cudaStream_t stream, uint64_t* launches);
-// dual.cu: the megakernel's scheduler with two paths per lane (RTB_PIPE_DUAL)
-int launch_dual(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
-                cudaStream_t stream, uint64_t* launches);
 int launch_wavefront(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
                      cudaStream_t stream, uint64_t* launches);
 

@@ -19,6 +19,33 @@
 
 namespace rtb {
 
+// ---- self-checks (-DRTB_DEBUG_CHECKS=1 builds only; compute-sanitizer is not available on the GPU pool) --------------
+// Every index the kernels form — traversal stack slots, node / primitive / material / texture / texel indices, shared
+// accumulation tiles, output pixels — is compared with its bound and violations are COUNTED per class in a device array
+// the host reads back (rtb_debug_check_failures).  Release builds compile the checks away.
+enum RtbCheck { RTB_CHK_STACK = 0, RTB_CHK_NODE = 1, RTB_CHK_PRIM = 2, RTB_CHK_MAT = 3, RTB_CHK_TEX = 4, RTB_CHK_TEXEL = 5,
+                RTB_CHK_TILE = 6, RTB_CHK_PIXEL = 7, RTB_CHK_QUEUE = 8, RTB_CHK_NAN = 9, RTB_CHK_COUNT = 16 };
+#if defined(RTB_DEBUG_CHECKS) && !defined(RTB_HOST_EMUL)
+// one counter array per translation unit (no relocatable device code in this build): each .cu reports its own kernels
+static __device__ unsigned int g_rtb_check_fail[RTB_CHK_COUNT];
+#define RTB_CHECK(cond, cls)                            \
+  do {                                                  \
+    if (!(cond)) atomicAdd(&g_rtb_check_fail[cls], 1u); \
+  } while (0)
+// each translation unit defines its reader once (render.cu, wavefront.cu, debug.cu); rtb_debug_check_failures adds them up
+#define RTB_DEFINE_CHECK_READER(fn)                                                                  \
+  int fn(unsigned int* acc) {                                                                        \
+    unsigned int h[RTB_CHK_COUNT];                                                                   \
+    if (cudaMemcpyFromSymbol(h, g_rtb_check_fail, sizeof h) != cudaSuccess) return -1;               \
+    for (int i = 0; i < RTB_CHK_COUNT; ++i) acc[i] += h[i], h[i] = 0;                                \
+    return cudaMemcpyToSymbol(g_rtb_check_fail, h, sizeof h) == cudaSuccess ? 0 : -1;                \
+  }
+#else
+#define RTB_CHECK(cond, cls) ((void)0)
+#define RTB_DEFINE_CHECK_READER(fn) \
+  int fn(unsigned int*) { return 0; }
+#endif
+
 // ---------------------------------------------------------------------------------------------
 struct V3f {
   float x, y, z;
@@ -385,11 +412,14 @@ RTB_DEV Hit trace_closest4(const SceneView& sv, const RayF& ray, float t_min, in
   for (;;) {
     while (cur >= 0) {
       if (kStats) cnt->node_tests += 2;
+      RTB_CHECK(cur < sv.n_nodes4, RTB_CHK_NODE);
       cur = node_step4(sv.nodes4, cur, ri, t_min, best.t, top);
+      RTB_CHECK(top >= stack && top <= stack + RTB_STACK_DEPTH, RTB_CHK_STACK);
     }
     if (cur == RTB_TRAVERSAL_END) return best;
     const unsigned code = ~(unsigned)cur;
     const int first = (int)(code >> 3), count = (int)(code & 7u);
+    RTB_CHECK(first >= 0 && first + count <= sv.n_prims, RTB_CHK_PRIM);
     for (int i = 0; i < count; ++i) {
       const int pi = first + i;
       float t;
@@ -417,8 +447,10 @@ RTB_DEV Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int
   for (;;) {
     while (cur >= 0) {
       if (kStats) cnt->node_tests++;
+      RTB_CHECK(cur < sv.n_nodes, RTB_CHK_NODE);
       int next, push;
       int nh = node_step(sv.nodes, cur, ri, t_min, best.t, &next, &push);
+      RTB_CHECK(sp >= 0 && sp < RTB_STACK_DEPTH, RTB_CHK_STACK);
       if (nh == 2) stack[sp++] = push;
       if (nh == 0) {
         if (sp == 0) return best;
@@ -463,12 +495,14 @@ RTB_DEV void sphere_uv(V3f n, float* u, float* v) {  // src/sphere.rs:9-15 (Q5: 
 RTB_DEV Surface finalize_hit(const SceneView& sv, const DPrim* __restrict__ prims, const RayF& ray,
                                                 const Hit& h, int4* mat_record = nullptr, bool force_uv = false) {
   Surface s;
+  RTB_CHECK(h.prim >= 0 && h.prim < sv.n_prims, RTB_CHK_PRIM);
   const float4 A = ldg4(&prims[h.prim].a);
   const float4 B = ldg4(&prims[h.prim].b);
   const int4 C = ldg4i(&prims[h.prim].c);
   const int type = RTB_PRIM_TYPE(C.x);
   const int xi = RTB_PRIM_XFORM(C.x);
   s.mat = C.y;
+  RTB_CHECK(C.y >= 0 && C.y < sv.n_mats, RTB_CHK_MAT);
   s.u = 0.0f, s.v = 0.0f;
   // the material record (type, texture, parameter, needs_uv) in one load, handed on to the caller
   const int4 mrec = __ldg(reinterpret_cast<const int4*>(sv.mats + C.y));
@@ -690,6 +724,7 @@ template <bool kStats>
 RTB_DEV V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p, TexCounters* tc) {
   for (;;) {
     // both halves of the 32-byte record at once: the colour load does not wait for the type test
+    RTB_CHECK(tex >= 0 && tex < sv.n_texs, RTB_CHK_TEX);
     const int4 hd = __ldg(reinterpret_cast<const int4*>(sv.texs + tex));
     const float4 col = __ldg(reinterpret_cast<const float4*>(sv.texs + tex) + 1);
     const int type = hd.x;
@@ -712,6 +747,7 @@ RTB_DEV V3f texture_value(const SceneView& sv, int tex, float u, float v, V3f p,
     int j = fj > 0.0f ? (int)fminf(fj, 2147483520.0f) : 0;
     if (i > nx - 1) i = nx - 1;
     if (j > ny - 1) j = ny - 1;
+    RTB_CHECK(i >= 0 && j >= 0 && hd.w >= 0 && hd.w + i + nx * j < sv.n_texels, RTB_CHK_TEXEL);
     uint32_t texel = __ldg(&sv.texels[hd.w + i + nx * j]);
     const float k = 1.0f / 255.0f;
     return mk((float)(texel & 255u) * k, (float)((texel >> 8) & 255u) * k, (float)((texel >> 16) & 255u) * k);

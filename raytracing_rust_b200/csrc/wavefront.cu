@@ -26,6 +26,9 @@
 
 namespace rtb {
 
+RTB_DEFINE_CHECK_READER(read_checks_wavefront)
+
+
 enum { WQ_LAMBERTIAN = 0, WQ_METAL, WQ_DIELECTRIC, WQ_LIGHT, WQ_ISOTROPIC, WQ_MISS, WQ_COUNT };
 
 struct WfCounters {
@@ -60,7 +63,7 @@ struct WfParams {
 };
 
 // append `slot` to a queue with one atomic per warp
-__device__ __forceinline__ void queue_push(int* __restrict__ q, int* __restrict__ count, int slot, bool pred) {
+__device__ __forceinline__ void queue_push(int* __restrict__ q, int* __restrict__ count, int slot, bool pred, int capacity) {
   const unsigned m = __ballot_sync(0xffffffffu, pred);  // callers keep whole warps converged here
   if (!pred) return;
   const int lane = threadIdx.x & 31;
@@ -68,6 +71,8 @@ __device__ __forceinline__ void queue_push(int* __restrict__ q, int* __restrict_
   int base = 0;
   if (lane == leader) base = atomicAdd(count, __popc(m));
   base = __shfl_sync(m, base, leader);
+  RTB_CHECK(base >= 0 && base + __popc(m) <= capacity && slot >= 0 && slot < capacity, RTB_CHK_QUEUE);
+  (void)capacity;
   q[base + __popc(m & ((1u << lane) - 1u))] = slot;
 }
 
@@ -99,7 +104,7 @@ __global__ void __launch_bounds__(256) k_wf_generate(WfView wv, DCamera cam, WfP
     wv.thr[slot] = make_float4(1.f, 1.f, 1.f, 0.f);
     wv.meta[slot] = make_int4((int)pixel, (int)sample, 0, -1);
   }
-  queue_push(wv.q_ext[parity], &wv.cnt->n_ext[parity], slot, live);
+  queue_push(wv.q_ext[parity], &wv.cnt->n_ext[parity], slot, live, wv.capacity);
 }
 
 // rolls the counters after an iteration: `consumed` extend queue emptied, shade queues emptied,
@@ -145,7 +150,7 @@ __global__ void __launch_bounds__(256) k_wf_extend(SceneView sv, WfView wv, WfPa
   }
   // one vote + one atomic per (warp, queue)
 #pragma unroll
-  for (int q = 0; q < WQ_COUNT; ++q) queue_push(wv.q_shade[q], &wv.cnt->n_shade[q], slot, on && which == q);
+  for (int q = 0; q < WQ_COUNT; ++q) queue_push(wv.q_shade[q], &wv.cnt->n_shade[q], slot, on && which == q, wv.capacity);
   const unsigned m_on = __ballot_sync(0xffffffffu, on);
   if (m_on && (threadIdx.x & 31) == 0) atomicAdd(&wv.cnt->segments, (unsigned long long)__popc(m_on));
 }
@@ -211,8 +216,8 @@ __global__ void __launch_bounds__(256) k_wf_shade(SceneView sv, WfView wv, WfPar
       atomicAdd(a + 2, rad.z);
     }
   }
-  queue_push(wv.q_ext[next_parity], &wv.cnt->n_ext[next_parity], slot, on && survive);
-  queue_push(wv.q_new, &wv.cnt->n_new, slot, on && !survive);
+  queue_push(wv.q_ext[next_parity], &wv.cnt->n_ext[next_parity], slot, on && survive, wv.capacity);
+  queue_push(wv.q_new, &wv.cnt->n_new, slot, on && !survive, wv.capacity);
 }
 
 __global__ void k_wf_init(WfView wv, unsigned long long total_paths) {

@@ -30,6 +30,22 @@ def test_secondary_ray_ids_with_self_exclusion_agree_with_oracle(rtb, orc, name)
         assert r["secondary"] >= 200_000, r  # not vacuous
 
 
+def test_closest_hit_hooks_agree_on_both_trees(rtb, orc, monkeypatch):
+    # the query kernels walk the upload-time choice of tree; RTB200_BVH_WIDTH forces either: same answers, ray by ray
+    nx = ny = 512
+    for name in ("final_scene", "random_scene", "cornell_box", "two_spheres"):
+        s, w, cam = rtb.Scene.named(name, nx, ny)
+        rays = rtb.primary_rays(cam, nx, ny, sample=4, seed=3)
+        p_ref, _ = orc.OracleScene(s.serialize(), w).closest_hit(rays)
+        got = {}
+        for width in ("2", "4"):
+            monkeypatch.setenv("RTB200_BVH_WIDTH", width)
+            got[width], _ = s.closest_hit_ex(w, rays)
+            assert float((got[width] == p_ref).mean()) >= 0.9999, (name, width)
+        monkeypatch.delenv("RTB200_BVH_WIDTH")
+        assert float((got["2"] == got["4"]).mean()) >= 0.99999
+
+
 # ---- HitRecord fields -------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", fc.ALL_SCENES)
 def test_hit_record_fields_match_oracle(rtb, orc, name):

@@ -252,13 +252,15 @@ def test_four_wide_tree_traces_the_same_paths_as_the_two_child_tree(rtb, name, b
     s, w, cam = rtb.Scene.named(name, nx, ny)
     o4 = rtb.default_opts(background=bg, seed=4, collect_stats=1)
     o2 = rtb.default_opts(background=bg, seed=4, collect_stats=1)
-    o2.reserved[6] = 2
+    o4.reserved[6], o2.reserved[6] = 4, 2  # force the tree; 0 = the upload-time choice (four-wide on small media-free scenes)
     a, _, sa = s.render(w, cam, nx, ny, ns, o4, want_rgb8=False, want_stats=True)
     b, _, sb = s.render(w, cam, nx, ny, ns, o2, want_rgb8=False, want_stats=True)
     for k in ("paths", "segments", "shade", "tex_evals", "medium_tests"):
         assert sa[k] == sb[k], (k, sa[k], sb[k])
     np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)
     assert sa["node_tests"] != sb["node_tests"]  # it really was the other tree
+    auto, _, sc = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, collect_stats=1), want_rgb8=False, want_stats=True)
+    assert sc["node_tests"] in (sa["node_tests"], sb["node_tests"]) and sc["segments"] == sa["segments"]
     print(name, "node tests (2-box units) per segment: 4-wide", sa["node_tests"] / sa["segments"], "2-wide", sb["node_tests"] / sb["segments"],
           "prim tests per segment", sa["prim_tests"] / sa["segments"], sb["prim_tests"] / sb["segments"])
 
@@ -275,53 +277,12 @@ def test_wavefront_small_capacity_and_sharding(rtb):
     _assert_same_estimate(a, b)
 
 
-# ---- 8. the shared-memory path pool (RTB_PIPE_POOL) computes the same estimator as the megakernel --------
-@pytest.mark.parametrize("name,bg,nx,ny", [("cornell_box", 0, 96, 64), ("final_scene_lit", 0, 96, 64), ("random_scene", 1, 96, 64),
-                                           ("cornell_smoke_book", 0, 96, 64), ("two_perlin_sphere", 1, 96, 64),
-                                           ("earth", 1, 37, 19), ("simple_light", 0, 250, 130)])
-def test_pool_equals_megakernel(rtb, name, bg, nx, ny):
-    # same counter-based draws, same device functions: only who runs which path when differs (ragged sizes too)
-    ns = 24
-    s, w, cam = rtb.Scene.named(name, nx, ny)
-    a, _, sa = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, pipeline=rtb.PIPE_MEGAKERNEL),
-                        want_rgb8=False, want_stats=True)
-    b, _, sb = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, pipeline=rtb.PIPE_POOL),
-                        want_rgb8=False, want_stats=True)
-    assert sa["segments"] == sb["segments"] and sb["paths"] == nx * ny * ns
-    _assert_same_estimate(a, b)
-
-
-def test_pool_sample_sharding_and_stats(rtb):
-    nx, ny, ns = 64, 48, 20
-    s, w, cam = rtb.Scene.named("cornell_box", nx, ny)
-    parts = []
-    for r in range(3):
-        o = rtb.default_opts(seed=9, pipeline=rtb.PIPE_POOL, sample_begin=r, sample_stride=3)
-        parts.append(s.render(w, cam, nx, ny, ns, o, want_rgb8=False)[0])
-    whole, _, st = s.render(w, cam, nx, ny, ns, rtb.default_opts(seed=9, pipeline=rtb.PIPE_POOL, collect_stats=1), want_rgb8=False,
-                            want_stats=True)
-    np.testing.assert_allclose(parts[0] + parts[1] + parts[2], whole, rtol=1e-4, atol=1e-4)
-    o_ref = rtb.default_opts(seed=9, pipeline=rtb.PIPE_MEGAKERNEL, collect_stats=1)
-    o_ref.reserved[6] = 2  # the two-child tree, the one the pool traverses (the megakernel's default is the four-wide tree)
-    ref, _, sr = s.render(w, cam, nx, ny, ns, o_ref, want_rgb8=False, want_stats=True)
-    assert st["node_tests"] == sr["node_tests"] and st["prim_tests"] == sr["prim_tests"] and st["shade"] == sr["shade"]
-
-
-# ---- 8b. two paths per lane (RTB_PIPE_DUAL): same draws, same device functions, same counters -------------------
-@pytest.mark.parametrize("name,bg,nx,ny", [("cornell_box", 0, 96, 64), ("final_scene_lit", 0, 96, 64), ("random_scene", 1, 93, 61),
-                                           ("cornell_smoke_book", 0, 96, 64), ("earth", 1, 37, 19)])
-def test_dual_equals_megakernel(rtb, name, bg, nx, ny):
-    ns = 24
-    s, w, cam = rtb.Scene.named(name, nx, ny)
-    kw = dict(background=bg, seed=4, collect_stats=1, sample_begin=1, sample_stride=2)
-    o_ref = rtb.default_opts(pipeline=rtb.PIPE_MEGAKERNEL, **kw)
-    o_ref.reserved[6] = 2  # the two-child tree, the one this pipeline traverses
-    a, _, sa = s.render(w, cam, nx, ny, ns, o_ref, want_rgb8=False, want_stats=True)
-    b, _, sb = s.render(w, cam, nx, ny, ns, rtb.default_opts(pipeline=rtb.PIPE_DUAL, **kw), want_rgb8=False, want_stats=True)
-    assert sb["paths"] == nx * ny * (ns // 2)
-    for k in ("segments", "node_tests", "prim_tests", "shade"):
-        assert sa[k] == sb[k], k
-    np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)  # identical paths; only the order of the float adds differs
+# ---- 8. the round-1 experiment pipelines are gone: asking for them is a loud error, not a silent fallback --------
+def test_removed_pipelines_are_errors(rtb):
+    s, w, cam = rtb.Scene.named("cornell_box", 16, 16)
+    for pipe in (rtb.PIPE_POOL, rtb.PIPE_DUAL):
+        with pytest.raises(rtb.RtbError):
+            s.render(w, cam, 16, 16, 2, rtb.default_opts(pipeline=pipe))
 
 
 def test_progressive_render_equals_one_shot_and_reports_progress(rtb):
