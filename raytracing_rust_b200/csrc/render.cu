@@ -142,6 +142,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
   int stack[RTB_STACK_DEPTH + 1];
   stack[0] = CUR_SHADE;
   int* top = stack + 1;
+#if defined(RTB_TOS_REG)
+  int tos = CUR_SHADE;  // (two-child tree only; the four-wide step keeps the plain memory stack)
+#endif
   int cur = CUR_WAIT;
   bool items_left = true;
   bool check_wait = true;  // warp-uniform
@@ -161,8 +164,13 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           if (kStats) cnt.node_tests++;
           int next, push;
           const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+#if defined(RTB_TOS_REG)  // experiment: the top of the stack lives in a register, so a pop's load is not waited for
+          if (nh == 2) { *top++ = tos; tos = push; }
+          if (nh == 0) { next = tos; tos = *--top; }
+#else
           if (nh == 2) *top++ = push;
           if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
+#endif
           cur = next;
         }
       }
@@ -175,8 +183,13 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           if (kStats) cnt.node_tests++;
           int next, push;
           const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+#if defined(RTB_TOS_REG)
+          if (nh == 2) { *top++ = tos; tos = push; }
+          if (nh == 0) { next = tos; tos = *--top; }
+#else
           if (nh == 2) *top++ = push;
           if (nh == 0) next = *--top;
+#endif
           cur = next;
         }
       }
@@ -333,6 +346,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
           top = stack + 1;
+#if defined(RTB_TOS_REG)
+          tos = CUR_SHADE;
+#endif
           cur = kWide ? sv.root4 : sv.root;
         }
       }
@@ -346,8 +362,13 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           if (kStats) cnt.node_tests++;
           int next, push;
           const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
+#if defined(RTB_TOS_REG)  // experiment: the top of the stack lives in a register, so a pop's load is not waited for
+          if (nh == 2) { *top++ = tos; tos = push; }
+          if (nh == 0) { next = tos; tos = *--top; }
+#else
           if (nh == 2) *top++ = push;
           if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
+#endif
           cur = next;
         }
       }
@@ -368,6 +389,9 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             best.t = t, best.prim = pi, best.face = face, best.id = id;
           }
         }
+#if defined(RTB_TOS_REG)
+        if (!kWide) { cur = tos; tos = *--top; } else
+#endif
         cur = *--top;
       }
     }

@@ -142,18 +142,32 @@ class ShardedExchange:
                 dist.all_gather_object(handles, (self.buf.peer_handle(), self.rgb8_buf.peer_handle()))
             else:
                 handles = [(None, None)]
-            for r in range(self.world):
-                if r == self.rank:
-                    self.ptrs.append(self.buf.ptr)
+            err = None
+            try:
+                for r in range(self.world):
+                    if r == self.rank:
+                        self.ptrs.append(self.buf.ptr)
+                    else:
+                        p = rtb.peer_open(handles[r][0], local_device)
+                        self._opened.append(p)
+                        self.ptrs.append(p)
+                if self.rank == root:
+                    self.root_rgb8_ptr = self.rgb8_buf.ptr
                 else:
-                    p = rtb.peer_open(handles[r][0], local_device)
-                    self._opened.append(p)
-                    self.ptrs.append(p)
-            if self.rank == root:
-                self.root_rgb8_ptr = self.rgb8_buf.ptr
-            else:
-                self.root_rgb8_ptr = rtb.peer_open(handles[root][1], local_device)
-                self._opened.append(self.root_rgb8_ptr)
+                    self.root_rgb8_ptr = rtb.peer_open(handles[root][1], local_device)
+                    self._opened.append(self.root_rgb8_ptr)
+            except Exception as e:  # e.g. no CUDA IPC / no peer path between two of the devices
+                err = e
+            if self.world > 1:
+                # the ranks agree on the outcome, so either all of them own a working exchange or all of them raise here
+                # (a rank that gave up alone would leave the others waiting in the next collective)
+                ok = torch.tensor([0 if err is not None else 1], device=dev)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+                if int(ok) == 0 and err is None:
+                    err = RuntimeError("peer mapping failed on another rank")
+            if err is not None:
+                self.close()
+                raise RuntimeError(f"ShardedExchange(p2p): {err}")
         else:
             self.rgb8_buf = None
             self.rgb8 = torch.empty(ny, nx, 3, dtype=torch.uint8, device=dev)
@@ -224,7 +238,10 @@ class ShardedExchange:
 
     def close(self):
         for p in self._opened:
-            self.rtb.peer_close(p)
+            try:
+                self.rtb.peer_close(p)
+            except Exception:
+                pass
         self._opened = []
         self.acc = None
         self.buf.free()

@@ -49,12 +49,12 @@ def check_self_hit_ids(backend_scene, oracle_scene, world, rays, rng, min_agree=
     p_ref, t_ref = oracle_scene.closest_hit(rays2, t_min=1e-3, media=False)
     p_dev, rec_dev = backend_scene.closest_hit_ex(world, rays2, self_id=self_id, t_min=1e-3)
     agree = float((p_ref == p_dev).mean())
-    out["agree"] = agree
+    out["agree"] = out["secondary_agree"] = agree
     out["rehit_self_ref"] = float((p_ref == self_id).mean())  # how often the ray meets its own primitive again (far root / other face)
     both = (p_ref == p_dev) & (p_ref >= 0)
     if both.any():
         rel = np.abs(rec_dev[both, 0] - t_ref[both]) / np.maximum(np.abs(t_ref[both]), 1e-3)
-        out["t_rel_q999"] = float(np.quantile(rel, 0.999))
+        out["t_rel_q999"] = out["secondary_t_rel_q999"] = float(np.quantile(rel, 0.999))
     assert agree >= min_agree, out
     return out
 

@@ -56,7 +56,9 @@ src_cache = {}
 def src(f, l):
     import glob
     if f not in src_cache:
-        c = glob.glob(f"/root/repo/**/{f}", recursive=True)
+        import os
+        root = os.environ.get("RTB_SRC_ROOT", "/root/repo")  # the tree the profiled binary was built from
+        c = glob.glob(f"{root}/**/{f}", recursive=True)
         src_cache[f] = open(c[0]).read().splitlines() if c else []
     L = src_cache[f]
     return L[l - 1].strip()[:90] if 0 < l <= len(L) else ""

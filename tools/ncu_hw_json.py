@@ -30,8 +30,9 @@ def scaled(name, unit_to):
 
 
 dur_s = scaled("gpu__time_duration.sum", 1.0)
-thread_inst = f("smsp__thread_inst_executed.sum")
 warp_inst = f("smsp__inst_executed.sum")
+ratio = f("smsp__thread_inst_executed_per_inst_executed.ratio")
+thread_inst = f("smsp__thread_inst_executed.sum") or (warp_inst * ratio if warp_inst and ratio else None)
 o = {
     "source": f"ncu --set full --clock-control none, one launch: {what}",
     "kernel": d.get("Kernel Name"),
@@ -48,7 +49,9 @@ o = {
     "pipe_lsu_pct": f("sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active"),
     "l1_hit_pct": f("l1tex__t_sector_hit_rate.pct"),
     "l2_hit_pct": f("lts__t_sector_hit_rate.pct"),
-    "lts__t_bytes": scaled("lts__t_bytes.sum", 1.0),
+    "lts__t_bytes": scaled("lts__t_bytes.sum", 1.0),  # not in --set full on this ncu; the two L1<->L2 figures below stand in
+    "l2_to_l1_read_bytes": scaled("l1tex__m_xbar2l1tex_read_bytes.sum", 1.0),
+    "l1_to_l2_write_bytes": scaled("l1tex__m_l1tex2xbar_write_bytes.sum", 1.0),
     "dram_bytes_read": scaled("dram__bytes_read.sum", 1.0),
     "dram_bytes_write": scaled("dram__bytes_write.sum", 1.0),
     "local_loads": f("sass__inst_executed_local_loads"),

@@ -43,8 +43,8 @@ print("|---|---:|---:|---:|---:|---:|---:|---:|---:|")
 for name, d in rows.items():
     if "secondary" not in d:
         continue
-    print(f"| {name} | {100 * d.get('primary_agree', float('nan')):.4f} % | {d['secondary']} | {100 * d['agree']:.4f} % | "
-          f"{100 * d.get('rehit_self_ref', 0):.1f} % | {d.get('t_rel_q999', 0):.1e} | {d.get('p_rel_q999', 0):.1e} / {d.get('p_rel_max', 0):.1e} | "
+    print(f"| {name} | {100 * d.get('primary_agree', float('nan')):.4f} % | {d['secondary']} | {100 * d.get('secondary_agree', d['agree']):.4f} % | "
+          f"{100 * d.get('rehit_self_ref', 0):.1f} % | {d.get('secondary_t_rel_q999', d.get('t_rel_q999', 0)):.1e} | {d.get('p_rel_q999', 0):.1e} / {d.get('p_rel_max', 0):.1e} | "
           f"{d.get('n_q999', 0):.1e} | {d.get('u_q999', 0):.1e} / {d.get('v_q999', 0):.1e} |")
 print("\n## Images: PSNR on the gamma-encoded [0,1] image the reference writes (tests/test.rs:71-78)\n")
 print("floor = oracle vs oracle (two seeds) at the same spp; GPU = GPU vs oracle at that spp; bias = GPU at 16x spp vs the mean of "
