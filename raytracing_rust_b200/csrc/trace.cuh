@@ -13,6 +13,7 @@
 #define RTB_DEV __device__ __forceinline__
 #endif
 
+
 #include "device_types.h"
 #include "philox.h"
 #include "rtb_scene_format.h"
