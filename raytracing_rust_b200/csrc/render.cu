@@ -633,9 +633,12 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
   const int my_bands = band_begin < bands_all ? (bands_all - band_begin + band_stride - 1) / band_stride : 0;
   const long long tiles = (long long)((nx + 7) / 8) * my_bands;
   if (tiles == 0) return RTB_OK;
-  // enough resident warps to fill the machine: split a pixel's samples over several threads
-  // when the image alone does not supply ~2 waves of warps
-  const long long want_warps = (long long)d->prop.multiProcessorCount * 64 * 2;
+  // Work items per launch: the persistent warps (SMs x blocks x 8) draw (tile x sample slice) items from a counter, so the
+  // launch ends with a tail of about one item per warp.  Keep >= ~24 items per resident warp by slicing a tile's samples:
+  // a small image — or one GPU's share of the rows under row-band sharding — otherwise hands every warp a few huge items
+  // (3840x2160 on 8 GPUs by bands: 9 items of 2 048 paths per warp, render 36.3 ms where the sample shards take 31.1).
+  static const int items_per_warp = std::getenv("RTB200_ITEMS_PER_WARP") ? std::max(1, std::atoi(std::getenv("RTB200_ITEMS_PER_WARP"))) : 24;
+  const long long want_warps = (long long)d->prop.multiProcessorCount * 24 * items_per_warp;
   const int chunk_max = 64;  // samples per pixel per launch: bounds kernel duration
   for (int done = 0; done < my_samples; done += chunk_max) {
     MegaParams P;
@@ -644,7 +647,7 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.sample_first = begin + done * stride;
     P.sample_step = stride;
     P.band_begin = band_begin, P.band_stride = band_stride;
-    int slices = (int)std::min<long long>(std::max<long long>(1, want_warps / std::max<long long>(1, tiles)), P.sample_count);
+    int slices = (int)std::min<long long>(std::max<long long>(1, (want_warps + tiles - 1) / std::max<long long>(1, tiles)), P.sample_count);
     P.slices = std::max(1, slices);
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
     P.keys = philox_keys(o.seed);
