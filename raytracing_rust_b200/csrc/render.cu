@@ -634,10 +634,10 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
   const long long tiles = (long long)((nx + 7) / 8) * my_bands;
   if (tiles == 0) return RTB_OK;
   // Work items per launch: the persistent warps (SMs x blocks x 8) draw (tile x sample slice) items from a counter, so the
-  // launch ends with a tail of about one item per warp.  Keep >= ~24 items per resident warp by slicing a tile's samples:
+  // launch ends with a tail of about one item per warp.  Keep >= ~12 items per resident warp by slicing a tile's samples (12 by measurement, profiles/r2_ab_items.txt):
   // a small image — or one GPU's share of the rows under row-band sharding — otherwise hands every warp a few huge items
   // (3840x2160 on 8 GPUs by bands: 9 items of 2 048 paths per warp, render 36.3 ms where the sample shards take 31.1).
-  static const int items_per_warp = std::getenv("RTB200_ITEMS_PER_WARP") ? std::max(1, std::atoi(std::getenv("RTB200_ITEMS_PER_WARP"))) : 24;
+  static const int items_per_warp = std::getenv("RTB200_ITEMS_PER_WARP") ? std::max(1, std::atoi(std::getenv("RTB200_ITEMS_PER_WARP"))) : 12;
   const long long want_warps = (long long)d->prop.multiProcessorCount * 24 * items_per_warp;
   const int chunk_max = 64;  // samples per pixel per launch: bounds kernel duration
   for (int done = 0; done < my_samples; done += chunk_max) {
