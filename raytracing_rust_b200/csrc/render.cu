@@ -639,7 +639,9 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
   // (3840x2160 on 8 GPUs by bands: 9 items of 2 048 paths per warp, render 36.3 ms where the sample shards take 31.1).
   static const int items_per_warp = std::getenv("RTB200_ITEMS_PER_WARP") ? std::max(1, std::atoi(std::getenv("RTB200_ITEMS_PER_WARP"))) : 12;
   const long long want_warps = (long long)d->prop.multiProcessorCount * 24 * items_per_warp;
-  const int chunk_max = 64;  // samples per pixel per launch: bounds kernel duration
+  // samples per pixel per launch: bounds kernel duration.  A row-band shard owns 1/band_stride of the pixels, so it takes
+  // band_stride times the samples per launch: the same paths per launch (and as few launch tails) as a sample shard
+  const int chunk_max = 64 * std::min(16, band_stride);
   for (int done = 0; done < my_samples; done += chunk_max) {
     MegaParams P;
     P.nx = nx, P.ny = ny, P.ns = ns;
