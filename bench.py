@@ -105,13 +105,19 @@ def cpu_reference_sample(seconds=15.0, nthreads=None, seed=11, scene_name=None, 
     """Times the CPU oracle (f64 restatement of the reference; the Rust original cannot be built
     here) on a bounded sample of the SAME workload: final_scene, same camera, 480x270, spp sized
     for ~`seconds` of wall time on `nthreads` host threads.  Returns (Mpaths/s, description, cores)."""
-    import raytracing_rust_b200 as rtb
     from oracle import oracle_py as orc
 
     nthreads = nthreads or os.cpu_count() or 1
     scene_name = scene_name or SCENE
-    s, w, cam = rtb.Scene.named(scene_name, nx, ny)
-    o = orc.OracleScene(s.serialize(), w)
+    if scene_name == "final_scene":
+        # the headline scene comes from committed bytes (tests/golden/final_scene.rtscene.head + assets/earthmap…rgb8) and the
+        # oracle's own camera struct: the reference arm loads liboracle.so only, nothing of the product
+        o = orc.OracleScene(orc.final_scene_bytes(), orc.FINAL_SCENE_WORLD)
+        cam = orc.final_scene_camera(nx, ny)
+    else:  # --configs-table rows: the other scenes are built through the product's scene constructors
+        import raytracing_rust_b200 as rtb
+        s, w, cam = rtb.Scene.named(scene_name, nx, ny)
+        o = orc.OracleScene(s.serialize(), w)
     t0 = time.perf_counter()
     o.render(cam, nx, ny, 1, seed=seed, nthreads=nthreads)  # calibration pass (also warms caches)
     per_spp = max(time.perf_counter() - t0, 1e-3)

@@ -39,6 +39,35 @@ lib.orc_camera_rays.argtypes = [_vp, _vp, _sz, _vp]
 lib.orc_sample.argtypes = [_i, _u64, _sz, _vp]
 
 
+class Camera(C.Structure):
+    """Camera::new arguments, src/camera.rs:21-31 (RtbCamera of include/rtb_scene_format.h): the oracle's own mirror, so that
+    a caller (bench.py --impl reference) needs nothing from the product package."""
+    _fields_ = [("look_from", C.c_double * 3), ("look_at", C.c_double * 3), ("view_up", C.c_double * 3),
+                ("vertical_fov", C.c_double), ("aspect", C.c_double), ("aperture", C.c_double),
+                ("focus_dist", C.c_double), ("time0", C.c_double), ("time1", C.c_double)]
+
+
+FINAL_SCENE_WORLD = 1415  # world handle inside tests/golden/final_scene.rtscene.head (tools/make_reference_fixture.py)
+
+
+def final_scene_bytes() -> bytes:
+    """final_scene as written (tests/test.rs:419-523) as .rtscene bytes, from committed files only: the table part
+    (tests/golden/final_scene.rtscene.head) + the decoded earthmap the scene's ImageTexture uses (assets/)."""
+    root = _HERE.parent
+    return (root / "tests" / "golden" / "final_scene.rtscene.head").read_bytes() + (root / "assets" / "earthmap_1024x512.rgb8").read_bytes()
+
+
+def final_scene_camera(nx: int, ny: int) -> Camera:
+    """set_camera of test_final_scene, tests/test.rs:819-830: (478,278,-600) -> (278,278,0), vfov 40, aspect nx/ny,
+    focus_dist 10, aperture 0.1, shutter [0,1]."""
+    c = Camera()
+    c.look_from[:] = (478.0, 278.0, -600.0)
+    c.look_at[:] = (278.0, 278.0, 0.0)
+    c.view_up[:] = (0.0, 1.0, 0.0)
+    c.vertical_fov, c.aspect, c.aperture, c.focus_dist, c.time0, c.time1 = 40.0, nx / ny, 0.1, 10.0, 0.0, 1.0
+    return c
+
+
 class OracleScene:
     """A scene loaded from the .rtscene bytes the product serialises (same bytes, same scene)."""
 
