@@ -293,6 +293,21 @@ int rtb_debug_scatter(rtb_scene*, int world, int mat, const double* in, size_t n
  * kind 1 = uniform in the unit disk (lens).  out = n x {x, y, z} floats. */
 int rtb_debug_sample(int kind, uint64_t seed, size_t n, int device, float* out);
 
+/* rtb_closest_hit_ex for callers that cannot allocate (no counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc).  The call makes
+ * NO allocation of any kind: inputs and outputs are DEVICE pointers of the caller — d_rays n x {o.xyz, d.xyz, time} floats,
+ * d_self_id n ints or NULL, d_out_prim n ints, d_out_rec n x 9 floats or NULL — and the one piece of scratch the query needs
+ * (the primitive-ID -> primitive table behind self_id) lives in a static device array of RTB_NOALLOC_MAX_PRIM_IDS entries
+ * (256 KB, held by every GPU that loads the library).  The scene must already be on its device (rtb_scene_upload, which does
+ * allocate, is the caller's set-up step; moving spheres are bounded for the shutter [0, 1]); scenes with more primitive IDs
+ * than the table holds are refused with RTB_ERR_INVALID.  Work is enqueued on `cuda_stream` (NULL = default stream) without
+ * synchronising.  Every call shares the one table: it is cleared and refilled per call, and two calls that overlap on the
+ * GPU (different streams, or different scenes from different threads) race on it — serialise them.
+ * Answers are those of rtb_closest_hit_ex on the same rays, bit for bit. */
+#define RTB_NOALLOC_MAX_PRIM_IDS 65536
+int rtb_closest_hit_noalloc(rtb_scene*, const float* d_rays, size_t n, double t_min, const int32_t* d_self_id,
+                            int32_t* d_out_prim, float* d_out_rec, void* cuda_stream);
+
 /* Self-checking builds (make NVEXTRA=-DRTB_DEBUG_CHECKS=1): every index the kernels form (traversal stack, node /
  * primitive / material / texture / texel, shared tiles, output pixels, wavefront queues) is bounds-checked on the device and
  * violations are counted per class; this reads and clears the 16 counters (all zero = clean).  The stand-in for

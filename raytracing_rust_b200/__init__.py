@@ -35,6 +35,7 @@ BVH_AUTO, BVH_HOST_SAH, BVH_DEVICE_LBVH = 0, 1, 2
 PIPE_AUTO, PIPE_MEGAKERNEL, PIPE_WAVEFRONT, PIPE_POOL, PIPE_DUAL = 0, 1, 2, 3, 4
 SHARD_SAMPLES, SHARD_BANDS = 0, 1
 BAND_ROWS = 4
+NOALLOC_MAX_PRIM_IDS = 65536
 
 NAMED_SCENES = (
     "random_scene", "two_spheres", "two_perlin_sphere", "earth", "simple_light",
@@ -146,6 +147,7 @@ _sig("rtb_debug_camera_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _i, _v
 _sig("rtb_debug_camera_draws", _i, _i, _i, _i, _u64, _vp)
 _sig("rtb_debug_scatter", _i, _vp, _i, _i, _vp, _sz, _u64, _i, _vp)
 _sig("rtb_debug_sample", _i, _i, _u64, _sz, _i, _vp)
+_sig("rtb_closest_hit_noalloc", _i, _vp, _vp, _sz, _d, _vp, _vp, _vp, _vp)
 _sig("rtb_debug_check_failures", _i, _i, C.POINTER(C.c_uint32))
 _sig("rtb_primary_rays", _i, C.POINTER(RtbCamera), _i, _i, _i, _u64, _vp)
 _sig("rtb_ppm_p3", _sz, _vp, _i, _i, _vp, _sz)
@@ -431,6 +433,12 @@ class Scene:
         _h(lib.rtb_closest_hit_ex(self._p, world, r.ctypes.data, n, t_min, sid.ctypes.data if sid is not None else None,
                                   device, prim.ctypes.data, rec.ctypes.data if want_rec else None), "closest_hit_ex")
         return prim, rec
+
+    def closest_hit_noalloc(self, d_rays_ptr: int, n: int, d_out_prim_ptr: int, d_out_rec_ptr: int = 0, d_self_id_ptr: int = 0,
+                            t_min=1e-3, stream: int = 0):
+        """rtb_closest_hit_noalloc: device pointers in and out, no allocation inside the call; the scene must be uploaded."""
+        _h(lib.rtb_closest_hit_noalloc(self._p, d_rays_ptr, n, t_min, d_self_id_ptr or None, d_out_prim_ptr, d_out_rec_ptr or None,
+                                       stream or None), "closest_hit_noalloc")
 
     def scatter(self, world, mat, inp: np.ndarray, seed=1, device=0):
         """rtb_debug_scatter: inp [n,16] {ray o,d,time, hit t,u,v,p,normal}; returns [n,10] {ok, o, d, atten}."""

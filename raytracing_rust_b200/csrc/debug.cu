@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -246,3 +247,63 @@ int rtb_debug_sample(int kind, uint64_t seed, size_t n, int device, float* out) 
 }
 
 }  // extern "C"
+
+// ---- closest-hit query that allocates nothing (rtb_closest_hit_noalloc) ------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  rtb_closest_hit_ex needs one piece of device
+// scratch — the table "primitive ID -> index into prims" that turns a ray's self_id into the primitive it leaves — and
+// allocates it (plus staging for its host buffers) per call.  Here the caller passes DEVICE inputs and outputs and the
+// table lives in a file-scope array every GPU that loads the library holds until exit: RTB_NOALLOC_MAX_PRIM_IDS ints =
+// 256 KB.  In host code `g_noalloc_id_table` is only a stand-in for the symbol: its device address is fetched once per
+// device with cudaGetSymbolAddress (that device current) and it is that pointer the kernels receive.
+namespace rtb {
+static __device__ __align__(256) int g_noalloc_id_table[RTB_NOALLOC_MAX_PRIM_IDS];
+
+namespace {
+const int kNoallocMaxDevices = 64;
+int* g_noalloc_table_ptr[kNoallocMaxDevices];  // device address of the array on each device, nullptr = not fetched yet
+std::mutex g_noalloc_mutex;
+
+// once per device, with that device current
+cudaError_t noalloc_table_for_current_device(int device, int** out) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mutex);
+  if (!g_noalloc_table_ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_id_table);
+    if (e != cudaSuccess) return e;
+    g_noalloc_table_ptr[device] = (int*)p;
+  }
+  *out = g_noalloc_table_ptr[device];
+  return cudaSuccess;
+}
+}  // namespace
+}  // namespace rtb
+
+extern "C" int rtb_closest_hit_noalloc(rtb_scene* s, const float* d_rays, size_t n, double t_min, const int32_t* d_self_id,
+                                       int32_t* d_out_prim, float* d_out_rec, void* cuda_stream) {
+  if (!s || (n && (!d_rays || !d_out_prim))) return fail(RTB_ERR_INVALID, "closest_hit_noalloc: bad argument");
+  if (!s->dev)  // uploading allocates: it is the caller's set-up step (rtb_scene_upload), not this call's
+    return fail(RTB_ERR_INVALID, "closest_hit_noalloc: scene not uploaded (call rtb_scene_upload first; this entry point allocates nothing)");
+  const DeviceScene* d = s->dev;
+  const int n_ids = d->flat.n_prim_ids;
+  if (n_ids > RTB_NOALLOC_MAX_PRIM_IDS)
+    return fail(RTB_ERR_INVALID, "closest_hit_noalloc: the scene has " + std::to_string(n_ids) + " primitive IDs, the static scratch table holds " +
+                                     std::to_string(RTB_NOALLOC_MAX_PRIM_IDS) + " (RTB_NOALLOC_MAX_PRIM_IDS); use rtb_closest_hit_ex");
+  if (d->device < 0 || d->device >= kNoallocMaxDevices) return fail(RTB_ERR_INVALID, "closest_hit_noalloc: device ordinal out of range");
+  if (n == 0) return RTB_OK;
+  CUDA_TRY(cudaSetDevice(d->device));
+  int* table = nullptr;
+  CUDA_TRY(noalloc_table_for_current_device(d->device, &table));
+  cudaStream_t stream = (cudaStream_t)cuda_stream;
+  if (d_self_id) {
+    // the array is shared by every call and keeps the last call's contents: start from zeros, then fill this scene's IDs
+    CUDA_TRY(cudaMemsetAsync(table, 0, (size_t)std::max(1, n_ids) * sizeof(int), stream));
+    if (d->view.n_prims > 0)
+      k_id_table<<<(d->view.n_prims + 255) / 256, 256, 0, stream>>>(d->view.prims, d->view.n_prims, table, n_ids);
+  }
+  k_closest_hit_ex<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(view_with_width(d, 0), d_rays, n, (float)t_min, d_self_id, table,
+                                                                     d_out_prim, d_out_rec);
+  CUDA_TRY(cudaGetLastError());
+  return RTB_OK;
+}
+

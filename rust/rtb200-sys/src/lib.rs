@@ -163,6 +163,8 @@ extern "C" {
     pub fn rtb_debug_sample(kind: c_int, seed: u64, n: usize, device: c_int, out: *mut f32) -> c_int;
     pub fn rtb_debug_texture_value(s: *mut rtb_scene, world: c_int, tex: c_int, uvp: *const f64, n: usize, device: c_int, out: *mut f32) -> c_int;
     pub fn rtb_philox4x32_10(counter: *const u32, key: *const u32, out: *mut u32) -> c_int;
+    pub fn rtb_closest_hit_noalloc(s: *mut rtb_scene, d_rays: *const f32, n: usize, t_min: c_double, d_self_id: *const i32, d_out_prim: *mut i32,
+                                   d_out_rec: *mut f32, stream: *mut c_void) -> c_int;
     pub fn rtb_debug_check_failures(device: c_int, out: *mut u32) -> c_int;
     pub fn rtb_issue_peak(device: c_int, fma_tlane_per_s: *mut f64, mixed_tlane_per_s: *mut f64, slab_tlane_per_s: *mut f64) -> c_int;
 }
