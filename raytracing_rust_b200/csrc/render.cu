@@ -490,11 +490,60 @@ SceneView view_with_width(const DeviceScene* d, int width) {
   return v;
 }
 
+// Scene tables come from a small per-device pool of device allocations, keyed by size: a caller that builds a fresh scene per
+// image (bench.py's e2e leg, a Rust #[test] per scene) otherwise pays a cudaMalloc per table and a cudaFree — which
+// synchronises the device — per table on every image; the pool made the occasional 50 ms "table uploads" and 20 ms scene
+// destructions of profiles/r2_e2e_stall_hunt_before.txt go away.  At most kPoolMaxBytes stay cached per device;
+// rtb_release_workspace() frees them.
+namespace {
+std::mutex g_pool_mutex;
+std::map<int, std::multimap<size_t, void*>> g_pool;
+std::map<int, size_t> g_pool_bytes;
+const size_t kPoolMaxBytes = (size_t)64 << 20;
+
+cudaError_t pool_alloc(int device, size_t bytes, void** out) {
+  {
+    std::lock_guard<std::mutex> lk(g_pool_mutex);
+    auto& m = g_pool[device];
+    auto it = m.find(bytes);
+    if (it != m.end()) {
+      *out = it->second;
+      g_pool_bytes[device] -= bytes;
+      m.erase(it);
+      return cudaSuccess;
+    }
+  }
+  return cudaMalloc(out, bytes);
+}
+void pool_free(int device, void* p, size_t bytes) {
+  {
+    std::lock_guard<std::mutex> lk(g_pool_mutex);
+    if (g_pool_bytes[device] + bytes <= kPoolMaxBytes) {
+      g_pool[device].emplace(bytes, p);
+      g_pool_bytes[device] += bytes;
+      return;
+    }
+  }
+  cudaFree(p);
+}
+void pool_release_all() {  // caller restores the current device
+  std::lock_guard<std::mutex> lk(g_pool_mutex);
+  for (auto& kv : g_pool) {
+    cudaSetDevice(kv.first);
+    for (auto& e : kv.second) cudaFree(e.second);
+    kv.second.clear();
+    g_pool_bytes[kv.first] = 0;
+  }
+}
+}  // namespace
+
 void destroy_device_scene(DeviceScene* d) {
   if (!d) return;
   int prev = 0;
   cudaGetDevice(&prev);
   cudaSetDevice(d->device);
+  if (!d->pooled.empty()) cudaDeviceSynchronize();  // what cudaFree did implicitly: nothing in flight may still read the tables
+  for (auto& e : d->pooled) pool_free(d->device, e.first, e.second);
   for (void* p : d->allocs) cudaFree(p);
   if (d->wf) destroy_wavefront_state(d->wf);
   cudaSetDevice(prev);
@@ -505,8 +554,8 @@ template <class T>
 static int upload_vec(DeviceScene* d, const std::vector<T>& v, const T** out) {
   void* p = nullptr;
   size_t bytes = std::max<size_t>(v.size() * sizeof(T), 16);
-  CUDA_TRY(cudaMalloc(&p, bytes));
-  d->allocs.push_back(p);
+  CUDA_TRY(pool_alloc(d->device, bytes, &p));
+  d->pooled.emplace_back(p, bytes);
   if (!v.empty()) CUDA_TRY(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
   *out = (const T*)p;
   return RTB_OK;
@@ -572,12 +621,12 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   v.n_nodes4 = (int)f.nodes4.size(), v.n_mats = (int)f.mats.size(), v.n_texs = (int)f.texs.size(), v.n_texels = (int)f.texels.size();
   v.root = f.root;
   void* st = nullptr;
-  CUDA_TRY(cudaMalloc(&st, 32 * sizeof(unsigned long long)));
-  d->allocs.push_back(st);
+  CUDA_TRY(pool_alloc(device, 32 * sizeof(unsigned long long), &st));
+  d->pooled.emplace_back(st, 32 * sizeof(unsigned long long));
   d->d_stats = (unsigned long long*)st;
   void* wk = nullptr;
-  CUDA_TRY(cudaMalloc(&wk, 64));
-  d->allocs.push_back(wk);
+  CUDA_TRY(pool_alloc(device, 64, &wk));
+  d->pooled.emplace_back(wk, (size_t)64);
   d->d_work = (unsigned int*)wk;
   tm.lap("small allocs");
   // only the SM count is used; cudaGetDeviceProperties costs 2-4 ms per call
@@ -860,8 +909,14 @@ struct Workspace {
   size_t sum_bytes = 0;
   void* rgb = nullptr;
   size_t rgb_bytes = 0;
+  // two pinned host slots the outputs travel through (copy_out): the caller's own buffers are never registered with
+  // CUDA — cudaHostRegister / cudaHostUnregister of a 25 MB buffer per call stalled for up to 1.5 s now and then
+  // (profiles/r2_e2e_stall_hunt_before.txt; the r1 verdict's N = 8 first-call stall)
+  void* pinned = nullptr;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
   bool busy = false;
 };
+const size_t kStageChunk = (size_t)4 << 20;  // bytes per pinned slot
 std::mutex g_ws_mutex;
 std::map<int, Workspace> g_ws;
 
@@ -869,6 +924,8 @@ struct WorkspaceLease {
   int device;
   float* d_sum = nullptr;
   uint8_t* d_rgb8 = nullptr;
+  uint8_t* pinned = nullptr;  // 2 x kStageChunk, or nullptr (private lease: plain copies)
+  cudaEvent_t ev[2] = {nullptr, nullptr};
   bool cached = false;
   ~WorkspaceLease() {
     if (cached) {
@@ -903,37 +960,58 @@ cudaError_t lease_workspace(int device, size_t sum_bytes, size_t rgb_bytes, Work
     if ((e = cudaMalloc(&w.rgb, rgb_bytes)) != cudaSuccess) return e;
     w.rgb_bytes = rgb_bytes;
   }
+  if (!w.pinned) {  // once per device; failure only costs the pipelined copy
+    if (cudaHostAlloc(&w.pinned, 2 * kStageChunk, cudaHostAllocDefault) != cudaSuccess) w.pinned = nullptr, cudaGetLastError();
+    else if (cudaEventCreateWithFlags(&w.ev[0], cudaEventDisableTiming) != cudaSuccess ||
+             cudaEventCreateWithFlags(&w.ev[1], cudaEventDisableTiming) != cudaSuccess) {
+      cudaGetLastError();
+      cudaFreeHost(w.pinned);
+      w.pinned = nullptr;
+    }
+  }
   w.busy = true;
   L->cached = true, L->d_sum = (float*)w.sum, L->d_rgb8 = rgb_bytes ? (uint8_t*)w.rgb : nullptr;
+  L->pinned = (uint8_t*)w.pinned, L->ev[0] = w.ev[0], L->ev[1] = w.ev[1];
   return cudaSuccess;
 }
 
-// While the GPU renders, the host thread would only wait: a helper touches every page of the caller's output
-// buffer (a fresh allocation faults page by page inside the D2H copy otherwise: 4K rgb8, 6 ms instead of 1)
-// and pins it, so the copy at the end is one DMA at full PCIe rate.
+// Device -> caller's host buffer through the two pinned slots: chunk k's DMA runs while the host copies chunk k-1 out of the
+// other slot, so the caller's (pageable, possibly never touched) buffer sees plain memcpy and CUDA sees only pinned memory.
+cudaError_t copy_out(const WorkspaceLease& L, void* dst, const void* d_src, size_t bytes) {
+  if (!L.pinned) return cudaMemcpy(dst, d_src, bytes, cudaMemcpyDeviceToHost);
+  const size_t n_chunks = (bytes + kStageChunk - 1) / kStageChunk;
+  auto len = [&](size_t k) { return std::min(kStageChunk, bytes - k * kStageChunk); };
+  cudaError_t e;
+  for (size_t k = 0; k <= n_chunks; ++k) {
+    if (k < n_chunks) {  // slot k % 2 was emptied by the host at step k - 1 (chunk k - 2)
+      if ((e = cudaMemcpyAsync(L.pinned + (k & 1) * kStageChunk, (const uint8_t*)d_src + k * kStageChunk, len(k), cudaMemcpyDeviceToHost, 0)) != cudaSuccess) return e;
+      if ((e = cudaEventRecord(L.ev[k & 1], 0)) != cudaSuccess) return e;
+    }
+    if (k >= 1) {
+      if ((e = cudaEventSynchronize(L.ev[(k - 1) & 1])) != cudaSuccess) return e;
+      std::memcpy((uint8_t*)dst + (k - 1) * kStageChunk, L.pinned + ((k - 1) & 1) * kStageChunk, len(k - 1));
+    }
+  }
+  return cudaSuccess;
+}
+
+// While the GPU renders, the host thread would only wait: a helper touches every page of the caller's output buffer (a fresh
+// allocation otherwise faults page by page inside the copy-out: 4K rgb8, 6 ms instead of 1).  Host work only — no CUDA call.
 struct OutputStager {
   std::thread th;
-  bool pinned = false;
-  void* ptr = nullptr;
-  void start(int device, void* p, size_t bytes) {
-    ptr = p;
-    th = std::thread([this, device, p, bytes]() {
+  void start(void* p, size_t bytes) {
+    th = std::thread([p, bytes]() {
       // fault the pages in WITHOUT changing them: a failed render must leave the caller's buffer as it was.  (A never-touched
       // anonymous page reads through the shared zero page, so a read alone would not allocate it: write back what was read.)
       volatile uint8_t* b = (volatile uint8_t*)p;
       for (size_t i = 0; i < bytes; i += 4096) b[i] = b[i];
       if (bytes) b[bytes - 1] = b[bytes - 1];
-      if (cudaSetDevice(device) == cudaSuccess && cudaHostRegister(p, bytes, cudaHostRegisterDefault) == cudaSuccess) pinned = true;
-      else cudaGetLastError();
     });
   }
   void join() {
     if (th.joinable()) th.join();
   }
-  ~OutputStager() {
-    join();
-    if (pinned) cudaHostUnregister(ptr);
-  }
+  ~OutputStager() { join(); }
 };
 }  // namespace
 
@@ -946,8 +1024,12 @@ int rtb_release_workspace(void) {
     cudaSetDevice(kv.first);
     if (kv.second.sum) cudaFree(kv.second.sum);
     if (kv.second.rgb) cudaFree(kv.second.rgb);
+    if (kv.second.pinned) cudaFreeHost(kv.second.pinned);
+    for (cudaEvent_t e : kv.second.ev)
+      if (e) cudaEventDestroy(e);
     kv.second = Workspace();
   }
+  pool_release_all();
   cudaSetDevice(prev);
   return RTB_OK;
 }
@@ -970,10 +1052,10 @@ int rtb_render(rtb_scene* s, int world, const RtbCamera* camera, int nx, int ny,
   uint8_t* d_rgb8 = ws.d_rgb8;
   e = cudaMemsetAsync(d_sum, 0, n * sizeof(float), 0);
   if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
-  OutputStager stage_rgb8, stage_sum;  // joined (and unpinned) on every return path
+  OutputStager stage_rgb8, stage_sum;  // joined on every return path
   const size_t stage_min = (size_t)1 << 20;  // not worth a thread for small images
-  if (out_rgb8 && n >= stage_min) stage_rgb8.start(o.device, out_rgb8, n);
-  if (out_sum_rgb && n * sizeof(float) >= stage_min) stage_sum.start(o.device, out_sum_rgb, n * sizeof(float));
+  if (out_rgb8 && n >= stage_min) stage_rgb8.start(out_rgb8, n);
+  if (out_sum_rgb && n * sizeof(float) >= stage_min) stage_sum.start(out_sum_rgb, n * sizeof(float));
   tm.lap("device buffers + memset (async)");
   rc = rtb_render_device(s, camera, nx, ny, ns, &o, d_sum, nullptr, stats);
   if (rc != RTB_OK) return rc;
@@ -982,13 +1064,13 @@ int rtb_render(rtb_scene* s, int world, const RtbCamera* camera, int nx, int ny,
     rc = rtb_resolve_device(d_sum, nx, ny, ns, d_rgb8, nullptr);
     if (rc != RTB_OK) return rc;
     stage_rgb8.join();
-    e = cudaMemcpy(out_rgb8, d_rgb8, n, cudaMemcpyDeviceToHost);
+    e = copy_out(ws, out_rgb8, d_rgb8, n);
     if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
     tm.lap("resolve + D2H rgb8 (includes waiting for the render)");
   }
   if (out_sum_rgb) {
     stage_sum.join();
-    e = cudaMemcpy(out_sum_rgb, d_sum, n * sizeof(float), cudaMemcpyDeviceToHost);
+    e = copy_out(ws, out_sum_rgb, d_sum, n * sizeof(float));
     if (e != cudaSuccess) return fail(RTB_ERR_CUDA, cudaGetErrorString(e));
   }
   e = cudaDeviceSynchronize();

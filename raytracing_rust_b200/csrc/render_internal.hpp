@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <utility>
 #include <vector>
 
 #include "device_types.h"
@@ -17,7 +18,8 @@ struct DeviceScene {
   int device = 0;
   FlatScene flat;   // host copy of what was uploaded (bounds, counts)
   SceneView view{};  // device pointers
-  std::vector<void*> allocs;
+  std::vector<void*> allocs;                      // plain cudaMalloc'ed (device BVH builder)
+  std::vector<std::pair<void*, size_t>> pooled;  // from the per-device allocation pool (render.cu pool_alloc)
   unsigned long long* d_stats = nullptr;  // 32 counters
   unsigned int* d_work = nullptr;         // work-item counter of the running megakernel launch
   cudaDeviceProp prop{};
