@@ -49,7 +49,7 @@ void run_shard(Shard* sh, int world, const RtbCamera* cam, int nx, int ny, int n
   if (rc != RTB_OK) return bail(rc);
   const size_t bytes = (size_t)3 * nx * ny * sizeof(float);
   cudaError_t e = cudaSetDevice(sh->device);
-  if (e == cudaSuccess) e = cudaMalloc(&sh->d_sum, bytes);
+  if (e == cudaSuccess) e = pool_alloc(sh->device, bytes, (void**)&sh->d_sum);  // kept between calls: no 100 MB cudaMalloc / cudaFree per image
   if (e == cudaSuccess) e = cudaMemsetAsync(sh->d_sum, 0, bytes, 0);
   if (e != cudaSuccess) {
     fail(RTB_ERR_CUDA, std::string("render_multi: ") + cudaGetErrorString(e));
@@ -136,7 +136,8 @@ extern "C" int rtb_render_multi(rtb_scene* s, int world, const RtbCamera* camera
     for (Shard& sh : shards)
       if (sh.d_sum) {
         cudaSetDevice(sh.device);
-        cudaFree(sh.d_sum);
+        cudaDeviceSynchronize();
+        pool_free(sh.device, sh.d_sum, (size_t)3 * nx * ny * sizeof(float));
       }
   };
   for (Shard& sh : shards)
@@ -184,8 +185,8 @@ extern "C" int rtb_render_multi(rtb_scene* s, int world, const RtbCamera* camera
   std::vector<const float*> bufs(G);
   for (int i = 0; i < G; ++i) bufs[i] = shards[i].d_sum;
   if (cuda_ok(cudaSetDevice(root), "cudaSetDevice")) {
-    cuda_ok(cudaMalloc(&d_rgb8, n), "cudaMalloc(rgb8)");
-    if (rc == RTB_OK && out_sum_rgb && G > 1 && !bands) cuda_ok(cudaMalloc(&d_total, n * sizeof(float)), "cudaMalloc(total)");
+    cuda_ok(pool_alloc(root, n, (void**)&d_rgb8), "cudaMalloc(rgb8)");
+    if (rc == RTB_OK && out_sum_rgb && G > 1 && !bands) cuda_ok(pool_alloc(root, n * sizeof(float), (void**)&d_total), "cudaMalloc(total)");
     if (rc == RTB_OK && G == 1) {
       rc = bands ? rtb_resolve_bands_device(bufs[0], nx, ny, ns, 0, 1, d_rgb8, 0, nullptr)
                  : rtb_reduce_resolve_device(bufs.data(), 1, nx, ny, ns, nullptr, d_rgb8, nullptr);
@@ -241,8 +242,8 @@ extern "C" int rtb_render_multi(rtb_scene* s, int world, const RtbCamera* camera
     }
     if (rc == RTB_OK) cuda_ok(cudaDeviceSynchronize(), "cudaDeviceSynchronize");
     for (void* p : staging) cudaFree(p);
-    if (d_rgb8) cudaFree(d_rgb8);
-    if (d_total) cudaFree(d_total);
+    if (d_rgb8) pool_free(root, d_rgb8, n);
+    if (d_total) pool_free(root, d_total, n * sizeof(float));
   }
   cleanup();
   if (rc != RTB_OK) return fail(rc, err);

@@ -490,16 +490,17 @@ SceneView view_with_width(const DeviceScene* d, int width) {
   return v;
 }
 
-// Scene tables come from a small per-device pool of device allocations, keyed by size: a caller that builds a fresh scene per
+// Scene tables (and rtb_render_multi's per-shard buffers) come from a per-device pool of device allocations, keyed by size: a caller that builds a fresh scene per
 // image (bench.py's e2e leg, a Rust #[test] per scene) otherwise pays a cudaMalloc per table and a cudaFree — which
 // synchronises the device — per table on every image; the pool made the occasional 50 ms "table uploads" and 20 ms scene
-// destructions of profiles/r2_e2e_stall_hunt_before.txt go away.  At most kPoolMaxBytes stay cached per device;
+// destructions of profiles/r2_e2e_stall_hunt_before.txt go away.  At most kPoolMaxBytes stay cached per device (the current device must be `device` in both calls);
 // rtb_release_workspace() frees them.
 namespace {
 std::mutex g_pool_mutex;
 std::map<int, std::multimap<size_t, void*>> g_pool;
 std::map<int, size_t> g_pool_bytes;
-const size_t kPoolMaxBytes = (size_t)64 << 20;
+const size_t kPoolMaxBytes = (size_t)512 << 20;  // of 180 GB; holds the accumulation buffers of rtb_render_multi's shards too
+}  // namespace
 
 cudaError_t pool_alloc(int device, size_t bytes, void** out) {
   {
@@ -526,6 +527,7 @@ void pool_free(int device, void* p, size_t bytes) {
   }
   cudaFree(p);
 }
+namespace {
 void pool_release_all() {  // caller restores the current device
   std::lock_guard<std::mutex> lk(g_pool_mutex);
   for (auto& kv : g_pool) {

@@ -40,6 +40,10 @@ int read_checks_render(unsigned int* acc);
 int read_checks_wavefront(unsigned int* acc);
 int read_checks_debug(unsigned int* acc);
 
+// per-device pool of device allocations keyed by size (render.cu); `device` must be the current device
+cudaError_t pool_alloc(int device, size_t bytes, void** out);
+void pool_free(int device, void* p, size_t bytes);
+
 int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi);
 void make_device_camera(const RtbCamera& c, DCamera* out);
 int launch_wavefront(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,

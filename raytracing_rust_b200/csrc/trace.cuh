@@ -402,7 +402,7 @@ RTB_DEV int node_step4(const DNode4* __restrict__ nodes, int cur, const RayInv& 
 // The same query over the four-wide tree (DNode4), the form the megakernel's NODE / LEAF phases run.
 template <bool kStats>
 RTB_DEV Hit trace_closest4(const SceneView& sv, const RayF& ray, float t_min, int self_prim, int self_face, Counters* cnt,
-                           float t_max = CUDART_INF_F) {
+                           float t_max) {
   Hit best;
   best.t = t_max, best.prim = -1, best.face = 0, best.id = -1;
   const float inv_a = rcp_fast(dot(ray.d, ray.d));
@@ -437,7 +437,7 @@ RTB_DEV Hit trace_closest4(const SceneView& sv, const RayF& ray, float t_min, in
 
 template <bool kStats>
 RTB_DEV Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int self_prim,
-                                             int self_face, Counters* cnt, float t_max = CUDART_INF_F) {
+                                             int self_face, Counters* cnt, float t_max) {
   // t_max: only surfaces nearer than this are of interest (a ConstantMedium that already scattered the ray there)
   if (sv.nodes4) return trace_closest4<kStats>(sv, ray, t_min, self_prim, self_face, cnt, t_max);
   Hit best;
@@ -476,6 +476,11 @@ RTB_DEV Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int
     if (sp == 0) return best;
     cur = stack[--sp];
   }
+}
+
+template <bool kStats>
+RTB_DEV Hit trace_closest(const SceneView& sv, const RayF& ray, float t_min, int self_prim, int self_face, Counters* cnt) {
+  return trace_closest<kStats>(sv, ray, t_min, self_prim, self_face, cnt, CUDART_INF_F);
 }
 
 // ---- surface point ------------------------------------------------------------------------------
