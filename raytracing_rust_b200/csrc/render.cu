@@ -701,7 +701,10 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.sample_step = stride;
     P.band_begin = band_begin, P.band_stride = band_stride;
     int slices = (int)std::min<long long>(std::max<long long>(1, (want_warps + tiles - 1) / std::max<long long>(1, tiles)), P.sample_count);
-    P.slices = std::max(1, slices);
+    // ... and never more than 64 samples x 32 pixels per item (a row-band shard's launch carries band_stride x 64 samples)
+    const int max_item_samples = std::getenv("RTB200_ITEM_SAMPLES") ? std::max(1, std::atoi(std::getenv("RTB200_ITEM_SAMPLES"))) : 64;
+    slices = std::max(slices, (P.sample_count + max_item_samples - 1) / max_item_samples);
+    P.slices = std::max(1, std::min(slices, P.sample_count));
     P.max_depth = o.max_depth, P.t_min = (float)o.t_min, P.background = o.background, P.seed = o.seed;
     P.keys = philox_keys(o.seed);
     {  // media into the kernel parameters when all of them (<= 2) are bounded by one static sphere
