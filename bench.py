@@ -6,9 +6,12 @@
 
 Workload: the reference's final_scene (tests/test.rs:419-523) as written, camera of
 test_final_scene (tests/test.rs:819-830), at BASELINE.json's 3840x2160.  A *step* renders
-SPP_PER_STEP camera samples of every pixel on every rank (the 10k-spp image is 157 such steps
-per GPU at N=1); ranks take interleaved sample indices and one NCCL sum-reduce of the
-accumulation buffers closes the timed region at N>1 (weak scaling: per-GPU work is fixed).
+SPP_PER_STEP camera samples of every pixel on every rank (the 10k-spp image is 156 such steps
+per GPU at N=1); ranks take interleaved sample indices (or, --shard bands, 4-row image bands) and ONE
+exchange step closes the timed region at N>1: sharded over the ranks through peer memory (each GPU
+reduces + quantises 1/N of the image into rank 0's rgb8 buffer), NCCL reduce_scatter + gather as the
+fallback (weak scaling: per-GPU work is fixed).  `e2e` at N>1 is ONE combined image on rank 0's pinned
+host buffer per call, fresh scene handles on every rank, barrier to barrier.
 A *path* is one top-level color(ray, world, 0) call (tests/test.rs:69).
 Prints ONE JSON line (rank 0).
 """
