@@ -448,12 +448,21 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
   }
   std::vector<int> dev_index(b.nodes.size(), -1);
   int next = 0;
-  for (size_t i = 0; i < b.nodes.size(); ++i)
-    if (b.nodes[i].left >= 0) dev_index[i] = next++;  // creation order is DFS pre-order
+  {  // device indices in DFS pre-order from the root (the creation order, unless the tree was re-linked afterwards)
+    std::vector<int> st{root};
+    while (!st.empty()) {
+      const int i = st.back();
+      st.pop_back();
+      if (b.nodes[i].left < 0) continue;
+      dev_index[i] = next++;
+      st.push_back(b.nodes[i].right);
+      st.push_back(b.nodes[i].left);
+    }
+  }
   out->nodes.resize(next);
   for (size_t i = 0; i < b.nodes.size(); ++i) {
     const BuildNode& bn = b.nodes[i];
-    if (bn.left < 0) continue;
+    if (bn.left < 0 || dev_index[i] < 0) continue;
     const BuildNode& L = b.nodes[bn.left];
     const BuildNode& R = b.nodes[bn.right];
     float l0[3], h0[3], l1[3], h1[3];
