@@ -458,7 +458,8 @@ def run_gpu(args):
                  "lane-instructions (fixed cost table x device op counters of one step; a medium's two boundary queries are "
                  "priced once, as primitive tests) / kernel time. "
                  "MEASURED_PEAKS.json has no FP32 entry. traffic = dram bytes read + written by one launch of this "
-                 "workload (ncu): megabytes against the algorithmic image + scene tables, i.e. HBM is idle. "
+                 "workload (ncu --set full, profiles/r2_mega_hw_4k64.json): megabytes against the algorithmic image + scene tables, "
+                 "i.e. HBM is idle. "
                  "hardware = the ncu view of the same launch shape (profiles/), not measured in this run."),
         "segments_per_path": st["segments"] / st["paths"], "node_tests_per_segment": st["node_tests"] / st["segments"],
         "prim_tests_per_segment": st["prim_tests"] / st["segments"],
@@ -512,20 +513,12 @@ def ncu_hardware_view(nx, ny, spp):
 
 
 def ncu_traffic_bytes(nx, ny, spp):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one k_render_mega launch, from the committed ncu capture of
-    exactly this launch shape (profiles/r1_mega_traffic_4k64.csv: 3840x2160, 64 spp); None for any other shape."""
-    import csv
-    f = ROOT / "profiles" / "r2_mega_traffic_4k64.csv"
-    if not f.exists():
-        f = ROOT / "profiles" / "r1_mega_traffic_4k64.csv"
-    if (nx, ny, spp) != (3840, 2160, 64) or not f.exists():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one k_render_mega launch, from the committed `ncu --set full` capture of
+    exactly this launch shape (profiles/r2_mega_hw_4k64.json: 3840x2160, 64 spp); None for any other shape."""
+    hw = ncu_hardware_view(nx, ny, spp)
+    if not hw or hw.get("dram_bytes_read") is None or hw.get("dram_bytes_write") is None:
         return None
-    per_launch = {}
-    for r in csv.DictReader(l for l in open(f) if l.startswith('"')):
-        if r["Metric Name"].startswith("dram__bytes"):
-            per_launch.setdefault(r["ID"], 0.0)
-            per_launch[r["ID"]] += float(r["Metric Value"])
-    return sum(per_launch.values()) / len(per_launch) if per_launch else None
+    return float(hw["dram_bytes_read"]) + float(hw["dram_bytes_write"])
 
 
 def main():
