@@ -27,6 +27,16 @@ for name, nx, ny, ns in (("cornell_smoke_book", 37, 23, 6), ("final_scene_lit", 
     prim, rec = s.closest_hit_ex(w, rays, self_id=None)
     prim2, _ = s.closest_hit_ex(w, rays, self_id=np.maximum(prim, -1))
     print(name, "closest hit", int((s.closest_hit(w, rays)[0] >= 0).sum()), int((prim >= 0).sum()), int((prim2 >= 0).sum()), flush=True)
+# the no-allocation query (static device scratch)
+import torch
+d_rays = torch.from_numpy(rays.astype(np.float32)).cuda()
+d_self = torch.from_numpy(np.maximum(prim, -1).astype(np.int32)).cuda()
+d_prim = torch.empty(len(rays), dtype=torch.int32, device="cuda")
+d_rec = torch.empty(len(rays), 9, dtype=torch.float32, device="cuda")
+for _ in range(2):
+    s.closest_hit_noalloc(d_rays.data_ptr(), len(rays), d_prim.data_ptr(), d_rec.data_ptr(), d_self.data_ptr())
+torch.cuda.synchronize()
+print("closest_hit_noalloc", int((d_prim >= 0).sum()))
 # field-level hooks
 print("camera", float(rtb.device_camera_rays(cam, 16, 9).sum()), "samplers", float(rtb.device_sample(0, 1, 1000).sum()), float(rtb.device_sample(1, 1, 1000).sum()))
 s = rtb.Scene()
