@@ -31,6 +31,7 @@ lib.emu_sample.argtypes = [_i, _u64, _sz, _vp]
 lib.emu_camera_rays.argtypes = [_vp, _i, _i, _i, _u64, _vp]
 lib.emu_render.argtypes = [_vp, _vp, _i, _i, _i, _i, _d, _i, _u64, _i, _vp, _vp, _vp, _sz]
 lib.emu_wide_stats.argtypes = [_vp, _vp, _sz, _i, _i, _vp]
+lib.emu_wide_steps.argtypes = [_vp, _vp, _sz, _i, _i, _vp, _vp]
 
 
 class EmuScene:
@@ -83,6 +84,14 @@ class EmuScene:
         out = np.zeros(16, np.uint64)
         lib.emu_wide_stats(self._p, r.ctypes.data, r.shape[0], width, mode, out.ctypes.data)
         return out
+
+    def wide_steps(self, rays9, width, mode):
+        """wide_stats plus the node steps every ray took."""
+        r = np.ascontiguousarray(rays9, dtype=np.float32)
+        out = np.zeros(16, np.uint64)
+        steps = np.zeros(r.shape[0], np.uint16)
+        lib.emu_wide_steps(self._p, r.ctypes.data, r.shape[0], width, mode, out.ctypes.data, steps.ctypes.data)
+        return out, steps
 
 
 def device_camera_rays(cam, nx, ny, sample=0, seed=1, device=0):

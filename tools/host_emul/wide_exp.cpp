@@ -65,6 +65,8 @@ int collapse(const std::vector<DNode>& bvh2, int node2, Wide& w) {
 }
 }  // namespace
 
+static uint16_t* g_per_ray_steps = nullptr;  // optional: node steps of each ray (emu_wide_steps)
+
 extern "C" {
 
 // rays: n x {o, d, time, self_prim, self_face} (9 floats; the last two are ints stored as floats).
@@ -93,6 +95,7 @@ void emu_wide_stats(void* scene, const float* rays, size_t n, int width, int mod
     int stack[256];
     int sp = 0;
     int cur = 0;
+    const uint64_t steps_before = out[0];
     for (;;) {
       while (cur >= 0) {
         out[0]++;
@@ -146,7 +149,15 @@ void emu_wide_stats(void* scene, const float* rays, size_t n, int width, int mod
     }
   done:
     if (best.prim >= 0) out[4]++;
+    if (g_per_ray_steps) g_per_ray_steps[i] = (uint16_t)std::min<uint64_t>(out[0] - steps_before, 65535);
   }
+}
+
+// same, and also the node steps each ray took (steps[n])
+void emu_wide_steps(void* scene, const float* rays, size_t n, int width, int mode, uint64_t* out, uint16_t* steps) {
+  g_per_ray_steps = steps;
+  emu_wide_stats(scene, rays, n, width, mode, out);
+  g_per_ray_steps = nullptr;
 }
 
 }  // extern "C"
