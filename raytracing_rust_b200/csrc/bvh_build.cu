@@ -278,10 +278,6 @@ int build_bvh_device(DeviceScene* d) {
   d->view.prims = d_prims;
   d->view.n_nodes = n - 1;
   d->n_nodes_device = n - 1;
-  if (n - 1 >= 1) {  // root = node 0: its two boxes ride in the megakernel's parameters
-    BVH_TRY(cudaMemcpy(&d->root_node, d_nodes, sizeof(DNode), cudaMemcpyDeviceToHost));
-    d->root_node_valid = true;
-  }
   return RTB_OK;
 }
 

@@ -29,11 +29,6 @@ struct MegaParams {
   float4 cmedia_sphere[2];
   float cmedia_neg_inv_density[2];
   int cmedia_mat[2];
-  // The root node of the two-child tree (valid when root_step != 0): a segment's first traversal step runs where the
-  // segment starts, on constant-bank operands, instead of as the first round of the NODE phase.
-  int root_step;
-  float4 root_n0, root_n1, root_n2;
-  int4 root_n3;
 };
 
 __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {

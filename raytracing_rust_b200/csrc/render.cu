@@ -350,15 +350,6 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           tos = CUR_SHADE;
 #endif
           cur = kWide ? sv.root4 : sv.root;
-#if RTB_ROOT_STEP
-          if (!kWide && P.root_step) {  // the root's two boxes are kernel parameters: the first step costs no load and no NODE round
-            if (kStats) cnt.node_tests++;
-            int next, push;
-            const int nh = node_step_words(P.root_n0, P.root_n1, P.root_n2, P.root_n3, ri, P.t_min, CUDART_INF_F, &next, &push);
-            if (nh == 2) *top++ = push;
-            cur = nh == 0 ? CUR_SHADE : next;  // a ray that misses both halves of the world is a finished segment
-          }
-#endif
         }
       }
       check_wait = true;
@@ -631,7 +622,6 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
   v.n_nodes4 = (int)f.nodes4.size(), v.n_mats = (int)f.mats.size(), v.n_texs = (int)f.texs.size(), v.n_texels = (int)f.texels.size();
   v.root = f.root;
-  if (!device_bvh && f.root >= 0 && (size_t)f.root < f.nodes.size()) d->root_node = f.nodes[f.root], d->root_node_valid = true;
   void* st = nullptr;
   CUDA_TRY(pool_alloc(device, 32 * sizeof(unsigned long long), &st));
   d->pooled.emplace_back(st, 32 * sizeof(unsigned long long));
@@ -732,15 +722,6 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
         P.cmedia_mat[mi] = m.mat;
       }
     }
-    P.root_step = 0;
-#if RTB_ROOT_STEP
-    if (d->root_node_valid) {
-      const DNode& r = d->root_node;
-      P.root_step = 1;
-      P.root_n0 = make_float4(r.n0.x, r.n0.y, r.n0.z, r.n0.w), P.root_n1 = make_float4(r.n1.x, r.n1.y, r.n1.z, r.n1.w);
-      P.root_n2 = make_float4(r.n2.x, r.n2.y, r.n2.z, r.n2.w), P.root_n3 = make_int4(r.n3.x, r.n3.y, r.n3.z, r.n3.w);
-    }
-#endif
     // tuning knobs (opts.reserved[0..3]); defaults from the sweep in profiles/r1_mega_sweep.txt
     P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 4;
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;

@@ -25,8 +25,6 @@ struct DeviceScene {
   cudaDeviceProp prop{};
   WavefrontState* wf = nullptr;
   int n_nodes_device = 0;  // BVH nodes resident on the device (host- or device-built)
-  DNode root_node{};             // host copy of the two-child tree's root (kernel parameter of the megakernel's first step)
-  bool root_node_valid = false;  // false when the root is a leaf
   const DNode4* d_nodes4 = nullptr;  // the four-wide form of the tree (host builder only); view.nodes4 = this or nullptr
 };
 

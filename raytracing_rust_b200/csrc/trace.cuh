@@ -322,10 +322,17 @@ RTB_DEV RayInv make_ray_inv(const RayF& ray) {
   return r;
 }
 
-// The slab tests of one two-child node given its four words: returns the number of children hit (0, 1, 2);
-// *next = the child to visit next (the nearer one), *push = the other (valid when 2 is returned).
-RTB_DEV int node_step_words(const float4 n0, const float4 n1, const float4 n2, const int4 n3, const RayInv& ri, float t_min,
-                            float t_best, int* next, int* push) {
+// Tests both children of inner node `cur` against (t_min, t_best).  Returns the number of
+// children hit (0, 1, 2); *next = the child to visit next (the nearer one), *push = the other
+// (valid when 2 is returned).
+RTB_DEV int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
+                                         int* next, int* push) {
+  // two 256-bit loads (LDG.E.256.CONSTANT): (n0, n1) and (n2, n3)
+  const Ld256 h0v = ld256(reinterpret_cast<const Ld256*>(nodes + cur));
+  const Ld256 h1v = ld256(reinterpret_cast<const Ld256*>(nodes + cur) + 1);
+  const float4 n0 = make_float4(h0v.v[0], h0v.v[1], h0v.v[2], h0v.v[3]), n1 = make_float4(h0v.v[4], h0v.v[5], h0v.v[6], h0v.v[7]);
+  const float4 n2 = make_float4(h1v.v[0], h1v.v[1], h1v.v[2], h1v.v[3]);
+  const int4 n3 = make_int4(__float_as_int(h1v.v[4]), __float_as_int(h1v.v[5]), __float_as_int(h1v.v[6]), __float_as_int(h1v.v[7]));
   float c0lox = fmaf(n0.x, ri.idx, -ri.oodx), c0hix = fmaf(n0.y, ri.idx, -ri.oodx);
   float c0loy = fmaf(n0.z, ri.idy, -ri.oody), c0hiy = fmaf(n0.w, ri.idy, -ri.oody);
   float c0loz = fmaf(n2.x, ri.idz, -ri.oodz), c0hiz = fmaf(n2.y, ri.idz, -ri.oodz);
@@ -346,18 +353,6 @@ RTB_DEV int node_step_words(const float4 n0, const float4 n1, const float4 n2, c
   }
   *next = h0 ? c0 : c1;
   return (h0 || h1) ? 1 : 0;
-}
-
-// Tests both children of inner node `cur` against (t_min, t_best): node_step_words on the node fetched from memory.
-RTB_DEV int node_step(const DNode* __restrict__ nodes, int cur, const RayInv& ri, float t_min, float t_best,
-                                         int* next, int* push) {
-  // two 256-bit loads (LDG.E.256.CONSTANT): (n0, n1) and (n2, n3)
-  const Ld256 h0v = ld256(reinterpret_cast<const Ld256*>(nodes + cur));
-  const Ld256 h1v = ld256(reinterpret_cast<const Ld256*>(nodes + cur) + 1);
-  const float4 n0 = make_float4(h0v.v[0], h0v.v[1], h0v.v[2], h0v.v[3]), n1 = make_float4(h0v.v[4], h0v.v[5], h0v.v[6], h0v.v[7]);
-  const float4 n2 = make_float4(h1v.v[0], h1v.v[1], h1v.v[2], h1v.v[3]);
-  const int4 n3 = make_int4(__float_as_int(h1v.v[4]), __float_as_int(h1v.v[5]), __float_as_int(h1v.v[6]), __float_as_int(h1v.v[7]));
-  return node_step_words(n0, n1, n2, n3, ri, t_min, t_best, next, push);
 }
 
 // One step of the FOUR-wide tree (DNode4): tests the four child boxes of inner node `cur` against (t_min, t_best), pushes
