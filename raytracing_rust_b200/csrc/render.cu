@@ -142,9 +142,6 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
   int stack[RTB_STACK_DEPTH + 1];
   stack[0] = CUR_SHADE;
   int* top = stack + 1;
-#if defined(RTB_TOS_REG)
-  int tos = CUR_SHADE;  // (two-child tree only; the four-wide step keeps the plain memory stack)
-#endif
   int cur = CUR_WAIT;
   bool items_left = true;
   bool check_wait = true;  // warp-uniform
@@ -164,77 +161,52 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           if (kStats) cnt.node_tests++;
           int next, push;
           const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-#if defined(RTB_TOS_REG)  // experiment: the top of the stack lives in a register, so a pop's load is not waited for
-          if (nh == 2) { *top++ = tos; tos = push; }
-          if (nh == 0) { next = tos; tos = *--top; }
-#else
           if (nh == 2) *top++ = push;
           if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
-#endif
           cur = next;
         }
       }
-#if defined(RTB_NODE_UNROLL) && RTB_NODE_UNROLL == 2  // experiment: two steps per vote (profiles/r2_experiments.txt)
-      if (cur >= 0) {
-        if (kWide) {
-          if (kStats) cnt.node_tests += 2;
-          cur = node_step4(sv.nodes4, cur, ri, P.t_min, best.t, top);
-        } else {
-          if (kStats) cnt.node_tests++;
-          int next, push;
-          const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-#if defined(RTB_TOS_REG)
-          if (nh == 2) { *top++ = tos; tos = push; }
-          if (nh == 0) { next = tos; tos = *--top; }
-#else
-          if (nh == 2) *top++ = push;
-          if (nh == 0) next = *--top;
-#endif
-          cur = next;
-        }
-      }
-#endif
       RTB_CHECK(top >= stack && top <= stack + RTB_STACK_DEPTH, RTB_CHK_STACK);
       RTB_CHECK(cur < (kWide ? sv.n_nodes4 : sv.n_nodes), RTB_CHK_NODE);
       m_node = __ballot_sync(0xffffffffu, cur >= 0);
     }
     // waiting lanes can only be released (and new ones only appear) after a SHADE round: test then, not every round
     if (check_wait) {
-    check_wait = false;
-    const unsigned m_wait = __ballot_sync(0xffffffffu, cur == CUR_WAIT);
-    if (m_wait != 0u) {
-      // the current item is used up.  Its tile partner (the previous item) must have drained
-      // before that tile can be flushed and reused for the next item.
-      const int tid = tid_here(), wib = tid >> 5;
-      const int g = s_gen[wib];
-      const bool alive = cur != CUR_DONE && cur != CUR_WAIT && cur != CUR_NEW;
-      const unsigned m_old = __ballot_sync(0xffffffffu, alive && (COLD_I(6) >> 5) != g);
-      if (m_old == 0u) {
-        const int g2 = g ^ 1;
-        flush_tile(s_acc[wib][g2], s_item[wib][g2], P.nx, lane, accum);
-        int item = P.n_items;
-        if (items_left) {
-          if (lane == 0) item = (int)atomicAdd(work_counter, 1u);
-          item = __shfl_sync(0xffffffffu, item, 0);
-        }
-        items_left = item < P.n_items;
-        __syncwarp();
-        if (lane == 0) {
-          int4 info = make_int4(-1, 0, 0, 0);
+      check_wait = false;
+      const unsigned m_wait = __ballot_sync(0xffffffffu, cur == CUR_WAIT);
+      if (m_wait != 0u) {
+        // the current item is used up.  Its tile partner (the previous item) must have drained
+        // before that tile can be flushed and reused for the next item.
+        const int tid = tid_here(), wib = tid >> 5;
+        const int g = s_gen[wib];
+        const bool alive = cur != CUR_DONE && cur != CUR_WAIT && cur != CUR_NEW;
+        const unsigned m_old = __ballot_sync(0xffffffffu, alive && (COLD_I(6) >> 5) != g);
+        if (m_old == 0u) {
+          const int g2 = g ^ 1;
+          flush_tile(s_acc[wib][g2], s_item[wib][g2], P.nx, lane, accum);
+          int item = P.n_items;
           if (items_left) {
-            const int tile = item / P.slices, slice = item - tile * P.slices;
-            const int x0 = (tile % tiles_x) * 8, y0 = ((tile / tiles_x) * P.band_stride + P.band_begin) * 4;
-            const int w_t = min(8, P.nx - x0), n_pix = w_t * min(4, P.ny - y0);
-            const int my_count = slice < P.sample_count ? (P.sample_count - slice + P.slices - 1) / P.slices : 0;
-            info = make_int4(x0, y0, w_t | (n_pix << 8), slice);
-            s_gen[wib] = g2, s_pool[wib] = n_pix * my_count, s_next[wib] = 0;
+            if (lane == 0) item = (int)atomicAdd(work_counter, 1u);
+            item = __shfl_sync(0xffffffffu, item, 0);
           }
-          s_item[wib][g2] = info;
+          items_left = item < P.n_items;
+          __syncwarp();
+          if (lane == 0) {
+            int4 info = make_int4(-1, 0, 0, 0);
+            if (items_left) {
+              const int tile = item / P.slices, slice = item - tile * P.slices;
+              const int x0 = (tile % tiles_x) * 8, y0 = ((tile / tiles_x) * P.band_stride + P.band_begin) * 4;
+              const int w_t = min(8, P.nx - x0), n_pix = w_t * min(4, P.ny - y0);
+              const int my_count = slice < P.sample_count ? (P.sample_count - slice + P.slices - 1) / P.slices : 0;
+              info = make_int4(x0, y0, w_t | (n_pix << 8), slice);
+              s_gen[wib] = g2, s_pool[wib] = n_pix * my_count, s_next[wib] = 0;
+            }
+            s_item[wib][g2] = info;
+          }
+          __syncwarp();
+          if (cur == CUR_WAIT) cur = items_left ? CUR_NEW : CUR_DONE;
         }
-        __syncwarp();
-        if (cur == CUR_WAIT) cur = items_left ? CUR_NEW : CUR_DONE;
       }
-    }
     }
     const unsigned m_leaf = __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
     const unsigned m_shade = __ballot_sync(0xffffffffu, cur == CUR_SHADE || cur == CUR_NEW);
@@ -346,9 +318,6 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
           top = stack + 1;
-#if defined(RTB_TOS_REG)
-          tos = CUR_SHADE;
-#endif
           cur = kWide ? sv.root4 : sv.root;
         }
       }
@@ -362,13 +331,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           if (kStats) cnt.node_tests++;
           int next, push;
           const int nh = node_step(sv.nodes, cur, ri, P.t_min, best.t, &next, &push);
-#if defined(RTB_TOS_REG)  // experiment: the top of the stack lives in a register, so a pop's load is not waited for
-          if (nh == 2) { *top++ = tos; tos = push; }
-          if (nh == 0) { next = tos; tos = *--top; }
-#else
           if (nh == 2) *top++ = push;
           if (nh == 0) next = *--top;  // the bottom entry is CUR_SHADE: an empty stack ends the traversal
-#endif
           cur = next;
         }
       }
@@ -389,9 +353,6 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             best.t = t, best.prim = pi, best.face = face, best.id = id;
           }
         }
-#if defined(RTB_TOS_REG)
-        if (!kWide) { cur = tos; tos = *--top; } else
-#endif
         cur = *--top;
       }
     }
