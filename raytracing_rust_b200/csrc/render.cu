@@ -101,11 +101,12 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
                                                         unsigned int* __restrict__ work_counter) {
   // Two accumulation tiles per warp: generation g of the warp's item sequence adds into s_acc[.][g & 1],
   // so paths of the previous item may still be in flight while the next item's paths start.
-  __shared__ float s_acc[8][2][96];
-  __shared__ int s_next[8];      // next path id of the current item
-  __shared__ int4 s_item[8][2];  // work item behind each accumulation tile: (x0, y0, w_t | n_pix << 8, slice); x0 < 0: none
-  __shared__ int s_gen[8];       // which tile the current item uses
-  __shared__ int s_pool[8];      // paths in the current item
+  constexpr int kWarps = kThreads / 32;  // warps never synchronise with each other: the block size only sets the register cap
+  __shared__ float s_acc[kWarps][2][96];
+  __shared__ int s_next[kWarps];      // next path id of the current item
+  __shared__ int4 s_item[kWarps][2];  // work item behind each accumulation tile: (x0, y0, w_t | n_pix << 8, slice); x0 < 0: none
+  __shared__ int s_gen[kWarps];       // which tile the current item uses
+  __shared__ int s_pool[kWarps];      // paths in the current item
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
   const int tiles_x = (P.nx + 7) >> 3;
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
   best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
   // Path state only the SHADE phase touches is parked in shared memory (s_cold[word][thread],
   // conflict-free) so the traversal loops do not carry it in registers or spill around it.
-  __shared__ float s_cold[7][256];
+  __shared__ float s_cold[7][kThreads];
 #define COLD_F(w) s_cold[w][tid]
 #define COLD_I(w) reinterpret_cast<int*>(s_cold[w])[tid]
   {
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
             rad = thr * background_color(P.background, ray.d);  // miss, src/color.rs:17-22
           }
           if (rad.x != 0.f || rad.y != 0.f || rad.z != 0.f) {
-            RTB_CHECK(pix_local >= 0 && pix_local < 64 && wib >= 0 && wib < 8, RTB_CHK_TILE);
+            RTB_CHECK(pix_local >= 0 && pix_local < 64 && wib >= 0 && wib < kWarps, RTB_CHK_TILE);
             RTB_CHECK(rad.x == rad.x && rad.y == rad.y && rad.z == rad.z, RTB_CHK_NAN);
             float* a = &s_acc[wib][pix_local >> 5][(pix_local & 31) * 3];
             atomicAdd(a, rad.x);
@@ -634,6 +635,33 @@ void make_device_camera(const RtbCamera& c, DCamera* out) {
   out->lens_radius = (float)(c.aperture / 2.0);
 }
 
+struct MegaLaunch {
+  unsigned blocks;
+  cudaStream_t stream;
+  const SceneView* view;
+  const DCamera* cam;
+  const MegaParams* P;
+  float* d_sum;
+  unsigned long long* d_stats;
+  unsigned int* work_counter;
+  int carveout_override;  // opts.reserved[5] (experiments)
+};
+
+// One instantiation of the megakernel.  Shared-memory carveout: just what the resident blocks need (the kernel's static
+// arrays + 1 KB reserved per block), the rest of the 228 KB array stays L1 — the BVH (90 KB) and primitives (68 KB) live
+// there and throughput follows the L1 size (carveout 100 %: -21 %, profiles/r1_experiments.txt).
+template <bool ST, int TH, int MB, bool WD>
+static void launch_mega_as(const MegaLaunch& L) {
+  static const int carveout = [] {
+    cudaFuncAttributes a{};
+    if (cudaFuncGetAttributes(&a, k_render_mega<ST, TH, MB, WD>) != cudaSuccess) return 30;
+    return (int)std::min<size_t>(100, (MB * (a.sharedSizeBytes + 1024) * 100) / (228 * 1024) + 5);
+  }();
+  cudaFuncSetAttribute(k_render_mega<ST, TH, MB, WD>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                       L.carveout_override > 0 ? L.carveout_override : carveout);
+  k_render_mega<ST, TH, MB, WD><<<L.blocks, TH, 0, L.stream>>>(*L.view, *L.cam, *L.P, L.d_sum, L.d_stats, L.work_counter);
+}
+
 static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
                        cudaStream_t stream, uint64_t* launches) {
   const int stride = std::max(1, o.sample_stride);
@@ -691,44 +719,41 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     const long long items = tiles * P.slices;
     if (items > 0x7fffffffLL) return fail(RTB_ERR_INVALID, "render: image too large for one launch");
     P.n_items = (int)items;
-    // occupancy point (threads per block, blocks per SM -> register cap): 2..4 = 256-thread blocks
-    // (125 / 80 / 64 registers), 5..7 = 128-thread blocks (102 / 85 / 73 registers)
-    const int block = min_blocks >= 5 ? 128 : 256;
+    // occupancy point = (threads per block, blocks per SM) -> resident warps and register cap.  Warps are independent, so the
+    // block shape is free: 2..4 = 256-thread blocks (512 / 768 / 1 024 threads per SM at 123 / 80 / 64 registers),
+    // 5..7 = 128-thread blocks (640 / 768 / 896 at 96 / 80 / 72).  The register file is per scheduler (16 K each), so only
+    // multiples of four warps per SM are worth having: 25 warps put 7 on one scheduler and get the 28-warp register cap.
+    int block = 256, bps = min_blocks;
+    if (min_blocks >= 5 && min_blocks <= 7) block = 128;
+    else if (min_blocks < 2 || min_blocks > 7) bps = 3;
     const int wpb = block / 32;
     // persistent grid: exactly the warps that are resident at once; they draw items until none is left
-    const long long blocks = std::min<long long>((items + wpb - 1) / wpb, (long long)d->prop.multiProcessorCount * min_blocks);
+    const long long blocks = std::min<long long>((items + wpb - 1) / wpb, (long long)d->prop.multiProcessorCount * bps);
     unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
     CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
-    // Shared-memory carveout: just what the resident blocks need (13.3 KB static + 1 KB reserved each), the rest of the
-    // 228 KB array stays L1 — the BVH (90 KB) and primitives (68 KB) live there and throughput follows the L1 size
-    // (carveout 100 %: -21 %, profiles/r1_experiments.txt).  o.reserved[5] overrides for experiments.
-    const int carveout = o.reserved[5] > 0 ? o.reserved[5] : std::min(100, (min_blocks * (14 * 1024 + 1024) * 100) / (228 * 1024) + 5);
-#define RTB_LAUNCH_MEGA(ST, TH, MB, WD)                                                                               \
-  do {                                                                                                                \
-    cudaFuncSetAttribute(k_render_mega<ST, TH, MB, WD>, cudaFuncAttributePreferredSharedMemoryCarveout, carveout);    \
-    k_render_mega<ST, TH, MB, WD><<<(unsigned)blocks, TH, 0, stream>>>(view, cam, P, d_sum, d->d_stats, wc);          \
-  } while (0)
     // which tree: the upload-time choice (ensure_uploaded) unless opts.reserved[6] = 2 / 4 forces the two-child / four-wide
-    // one (A/B runs); the 128-thread occupancy points exist for the two-child tree only
+    // one (A/B runs); the four-wide tree has the 256-thread occupancy points only
     const SceneView view = view_with_width(d, o.reserved[6]);
     const bool wide = view.nodes4 != nullptr && block == 256;
+    const MegaLaunch L{(unsigned)blocks, stream, &view, &cam, &P, d_sum, d->d_stats, wc, o.reserved[5]};
     if (o.collect_stats) {
-      if (block == 256) { if (wide) RTB_LAUNCH_MEGA(true, 256, 2, true); else RTB_LAUNCH_MEGA(true, 256, 2, false); }
-      else RTB_LAUNCH_MEGA(true, 128, 4, false);
+      if (block != 256) launch_mega_as<true, 128, 4, false>(L);
+      else if (wide) launch_mega_as<true, 256, 2, true>(L);
+      else launch_mega_as<true, 256, 2, false>(L);
     } else if (wide) {
       switch (min_blocks) {
-        case 2: RTB_LAUNCH_MEGA(false, 256, 2, true); break;
-        case 4: RTB_LAUNCH_MEGA(false, 256, 4, true); break;
-        default: RTB_LAUNCH_MEGA(false, 256, 3, true); break;
+        case 2: launch_mega_as<false, 256, 2, true>(L); break;
+        case 4: launch_mega_as<false, 256, 4, true>(L); break;
+        default: launch_mega_as<false, 256, 3, true>(L); break;
       }
     } else {
       switch (min_blocks) {
-        case 2: RTB_LAUNCH_MEGA(false, 256, 2, false); break;
-        case 4: RTB_LAUNCH_MEGA(false, 256, 4, false); break;
-        case 5: RTB_LAUNCH_MEGA(false, 128, 5, false); break;
-        case 6: RTB_LAUNCH_MEGA(false, 128, 6, false); break;
-        case 7: RTB_LAUNCH_MEGA(false, 128, 7, false); break;
-        default: RTB_LAUNCH_MEGA(false, 256, 3, false); break;
+        case 2: launch_mega_as<false, 256, 2, false>(L); break;
+        case 4: launch_mega_as<false, 256, 4, false>(L); break;
+        case 5: launch_mega_as<false, 128, 5, false>(L); break;
+        case 6: launch_mega_as<false, 128, 6, false>(L); break;
+        case 7: launch_mega_as<false, 128, 7, false>(L); break;
+        default: launch_mega_as<false, 256, 3, false>(L); break;
       }
     }
     ++*launches;
