@@ -113,6 +113,7 @@ struct SceneView {
   int n_nodes, n_prims, n_media, root;  // root: node index (always an inner node)
   int root4;                            // root of nodes4
   int n_nodes4, n_mats, n_texs, n_texels;  // table sizes (the RTB_DEBUG_CHECKS build compares every index with them)
+  int flat;  // != 0: the megakernel scans `prims` instead of walking a tree (scenes of a handful of primitives)
 };
 
 struct DCamera {  // src/camera.rs:8-18, f32

@@ -398,6 +398,29 @@ int flatten_scene(const rtb_scene& s, int world, double time_lo, double time_hi,
     return fail(RTB_ERR_INVALID, "flatten: " + (w.err.empty() ? std::string("walk failed") : w.err));
 
   int n = (int)out->prims.size();
+  {  // FlatScene::enclosed: count the faces of the world box that a thin primitive (a wall) covers to >= 80 %
+    Box3 world_box;
+    for (const Box3& b : w.prim_boxes) world_box.grow(b);
+    int covered = 0;
+    for (int a = 0; a < 3 && n > 0; ++a) {
+      const int u = (a + 1) % 3, v = (a + 2) % 3;
+      const double ext = world_box.hi[a] - world_box.lo[a];
+      const double face = (world_box.hi[u] - world_box.lo[u]) * (world_box.hi[v] - world_box.lo[v]);
+      if (!(ext > 0.0) || !(face > 0.0)) continue;
+      for (int side = 0; side < 2; ++side) {
+        const double plane = side ? world_box.hi[a] : world_box.lo[a];
+        for (const Box3& b : w.prim_boxes) {
+          const bool thin = b.hi[a] - b.lo[a] <= 1e-3 * ext;
+          const bool there = std::fabs((side ? b.hi[a] : b.lo[a]) - plane) <= 1e-3 * ext;
+          if (thin && there && (b.hi[u] - b.lo[u]) * (b.hi[v] - b.lo[v]) >= 0.8 * face) {
+            ++covered;
+            break;
+          }
+        }
+      }
+    }
+    out->enclosed = covered >= 4;
+  }
   if (n == 0) {  // only media, or an empty list: nothing to traverse
     DNode dn{};  // two empty leaves
     dn.n0 = {0, 0, 0, 0}, dn.n1 = dn.n0, dn.n2 = dn.n0;

@@ -26,6 +26,9 @@ struct FlatScene {
   int bvh_depth = 0;
   double time_lo = 0.0, time_hi = 1.0;  // shutter range the moving-sphere bounds cover
   bool has_moving = false;
+  // >= 4 of the six faces of the scene's bounding box are covered by one thin primitive each (a room: cornell_box).  Rays
+  // inside such a scene always hit something, which moves the point where scanning all primitives beats walking a tree.
+  bool enclosed = false;
 };
 
 // Returns 0 or an RtbStatus error (message via set_error).

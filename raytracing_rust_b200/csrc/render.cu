@@ -95,12 +95,16 @@ __device__ __forceinline__ int tid_here() {
   return t;
 }
 
-template <bool kStats, int kThreads, int kMinBlocks, bool kWide>
+// kTree: how a segment finds its closest hit.  0 = the two-child BVH, 1 = the four-wide BVH, 2 = no tree: scenes of a handful
+// of primitives (the book scenes: two_spheres, cornell_box ...) test every primitive where the segment starts, in lock step, like
+// the reference's own HittableList::hit scan (src/hittable.rs:37-47) — no NODE / LEAF rounds, every live lane is always in SHADE.
+template <bool kStats, int kThreads, int kMinBlocks, int kTree>
 __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
                                                         unsigned long long* __restrict__ stats,
                                                         unsigned int* __restrict__ work_counter) {
   // Two accumulation tiles per warp: generation g of the warp's item sequence adds into s_acc[.][g & 1],
   // so paths of the previous item may still be in flight while the next item's paths start.
+  constexpr bool kWide = kTree == 1, kFlat = kTree == 2;
   constexpr int kWarps = kThreads / 32;  // warps never synchronise with each other: the block size only sets the register cap
   __shared__ float s_acc[kWarps][2][96];
   __shared__ int s_next[kWarps];      // next path id of the current item
@@ -151,8 +155,8 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
   // >= k_leaf lanes hold a leaf, otherwise SHADE once >= k_shade lanes wait for it; when no
   // phase reaches its threshold (drained pool, tiny scenes) the most populated one runs.
   for (;;) {
-    unsigned m_node = __ballot_sync(0xffffffffu, cur >= 0);
-    while (__popc(m_node) >= P.k_node) {
+    unsigned m_node = kFlat ? 0u : __ballot_sync(0xffffffffu, cur >= 0);
+    while (!kFlat && __popc(m_node) >= P.k_node) {
       // ------------------------------------------------------------------ NODE phase
       if (cur >= 0) {
         if (kWide) {  // four child boxes per step (DNode4); counted as two two-box tests
@@ -209,14 +213,16 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
         }
       }
     }
-    const unsigned m_leaf = __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
+    const unsigned m_leaf = kFlat ? 0u : __ballot_sync(0xffffffffu, cur < 0 && cur > CUR_DONE);
     const unsigned m_shade = __ballot_sync(0xffffffffu, cur == CUR_SHADE || cur == CUR_NEW);
     if ((m_node | m_leaf | m_shade) == 0u) break;  // (a waiting lane implies a live one, handled above)
-    const int n_node = __popc(m_node), n_leaf = __popc(m_leaf), n_shade_l = __popc(m_shade);
-    int phase;  // 0 node, 1 leaf, 2 shade
-    if (n_leaf >= P.k_leaf) phase = 1;
-    else if (n_shade_l >= P.k_shade) phase = 2;
-    else phase = (n_node >= n_leaf && n_node >= n_shade_l) ? 0 : (n_leaf >= n_shade_l ? 1 : 2);
+    int phase = 2;  // 0 node, 1 leaf, 2 shade
+    if (!kFlat) {
+      const int n_node = __popc(m_node), n_leaf = __popc(m_leaf), n_shade_l = __popc(m_shade);
+      if (n_leaf >= P.k_leaf) phase = 1;
+      else if (n_shade_l >= P.k_shade) phase = 2;
+      else phase = (n_node >= n_leaf && n_node >= n_shade_l) ? 0 : (n_leaf >= n_shade_l ? 1 : 2);
+    }
 
     if (phase == 2) {
       // ------------------------------------------------------------------ SHADE phase
@@ -318,11 +324,26 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           ri = make_ray_inv(ray);
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
-          top = stack + 1;
-          cur = kWide ? sv.root4 : sv.root;
+          if (kFlat) {  // the whole closest-hit query here: every primitive, same acceptance and tie rule as the LEAF phase
+            for (int pi = 0; pi < sv.n_prims; ++pi) {
+              float t;
+              int face, id;
+              if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, P.t_min, best.t, pi == self_prim, self_face, &t,
+                                         &face, &id, &cnt) &&
+                  (t < best.t || id > best.id)) {
+                best.t = t, best.prim = pi, best.face = face, best.id = id;
+              }
+            }
+            cur = CUR_SHADE;
+          } else {
+            top = stack + 1;
+            cur = kWide ? sv.root4 : sv.root;
+          }
         }
       }
       check_wait = true;
+    } else if (kFlat) {
+      // (no other phase exists without a tree)
     } else if (phase == 0) {
       if (cur >= 0) {  // below-threshold NODE step
         if (kWide) {
@@ -443,12 +464,18 @@ struct StageTimer {
 
 RTB_DEFINE_CHECK_READER(read_checks_render)
 
+// Largest scenes the megakernel scans linearly instead of walking a BVH, by measurement (profiles/r2_experiments.txt E19):
+// open scenes (rays mostly leave: the root miss of a tree is one step) up to 4 primitives, enclosed ones (FlatScene::enclosed,
+// every ray hits a wall) up to 16 — break-even at 6-8 and ~24.
+static const int kFlatMaxPrimsOpen = 4, kFlatMaxPrimsEnclosed = 16;
+
 SceneView view_with_width(const DeviceScene* d, int width) {
   SceneView v = d->view;
   if (width == 0)
     if (const char* e = std::getenv("RTB200_BVH_WIDTH")) width = std::atoi(e);
-  if (width == 2) v.nodes4 = nullptr;
-  else if (width == 4 && d->d_nodes4) v.nodes4 = d->d_nodes4;
+  if (width == 1) v.flat = 1;  // (a scene of any size: experiments and the same-paths test)
+  else if (width == 2) v.nodes4 = nullptr, v.flat = 0;
+  else if (width == 4 && d->d_nodes4) v.nodes4 = d->d_nodes4, v.flat = 0;
   return v;
 }
 
@@ -584,6 +611,11 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   v.n_prims = (int)f.prims.size(), v.n_media = (int)f.media.size();
   v.n_nodes4 = (int)f.nodes4.size(), v.n_mats = (int)f.mats.size(), v.n_texs = (int)f.texs.size(), v.n_texels = (int)f.texels.size();
   v.root = f.root;
+  {  // scenes of a handful of primitives are scanned, not traversed (k_render_mega kTree = 2); RTB200_FLAT_MAX overrides
+    static const int flat_max = std::getenv("RTB200_FLAT_MAX") ? std::atoi(std::getenv("RTB200_FLAT_MAX")) : -1;
+    const int limit = flat_max >= 0 ? flat_max : (f.enclosed ? kFlatMaxPrimsEnclosed : kFlatMaxPrimsOpen);
+    v.flat = (int)f.prims.size() <= limit ? 1 : 0;
+  }
   void* st = nullptr;
   CUDA_TRY(pool_alloc(device, 32 * sizeof(unsigned long long), &st));
   d->pooled.emplace_back(st, 32 * sizeof(unsigned long long));
@@ -650,7 +682,7 @@ struct MegaLaunch {
 // One instantiation of the megakernel.  Shared-memory carveout: just what the resident blocks need (the kernel's static
 // arrays + 1 KB reserved per block), the rest of the 228 KB array stays L1 — the BVH (90 KB) and primitives (68 KB) live
 // there and throughput follows the L1 size (carveout 100 %: -21 %, profiles/r1_experiments.txt).
-template <bool ST, int TH, int MB, bool WD>
+template <bool ST, int TH, int MB, int WD>
 static void launch_mega_as(const MegaLaunch& L) {
   static const int carveout = [] {
     cudaFuncAttributes a{};
@@ -731,29 +763,36 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     const long long blocks = std::min<long long>((items + wpb - 1) / wpb, (long long)d->prop.multiProcessorCount * bps);
     unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
     CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
-    // which tree: the upload-time choice (ensure_uploaded) unless opts.reserved[6] = 2 / 4 forces the two-child / four-wide
-    // one (A/B runs); the four-wide tree has the 256-thread occupancy points only
+    // which tree: the upload-time choice (ensure_uploaded) unless opts.reserved[6] = 1 / 2 / 4 forces the flat list / the
+    // two-child / the four-wide tree (A/B runs); flat and four-wide have the 256-thread occupancy points only
     const SceneView view = view_with_width(d, o.reserved[6]);
-    const bool wide = view.nodes4 != nullptr && block == 256;
+    const bool flat = view.flat != 0 && block == 256, wide = !flat && view.nodes4 != nullptr && block == 256;
     const MegaLaunch L{(unsigned)blocks, stream, &view, &cam, &P, d_sum, d->d_stats, wc, o.reserved[5]};
     if (o.collect_stats) {
-      if (block != 256) launch_mega_as<true, 128, 4, false>(L);
-      else if (wide) launch_mega_as<true, 256, 2, true>(L);
-      else launch_mega_as<true, 256, 2, false>(L);
+      if (block != 256) launch_mega_as<true, 128, 4, 0>(L);
+      else if (flat) launch_mega_as<true, 256, 2, 2>(L);
+      else if (wide) launch_mega_as<true, 256, 2, 1>(L);
+      else launch_mega_as<true, 256, 2, 0>(L);
+    } else if (flat) {
+      switch (min_blocks) {
+        case 2: launch_mega_as<false, 256, 2, 2>(L); break;
+        case 4: launch_mega_as<false, 256, 4, 2>(L); break;
+        default: launch_mega_as<false, 256, 3, 2>(L); break;
+      }
     } else if (wide) {
       switch (min_blocks) {
-        case 2: launch_mega_as<false, 256, 2, true>(L); break;
-        case 4: launch_mega_as<false, 256, 4, true>(L); break;
-        default: launch_mega_as<false, 256, 3, true>(L); break;
+        case 2: launch_mega_as<false, 256, 2, 1>(L); break;
+        case 4: launch_mega_as<false, 256, 4, 1>(L); break;
+        default: launch_mega_as<false, 256, 3, 1>(L); break;
       }
     } else {
       switch (min_blocks) {
-        case 2: launch_mega_as<false, 256, 2, false>(L); break;
-        case 4: launch_mega_as<false, 256, 4, false>(L); break;
-        case 5: launch_mega_as<false, 128, 5, false>(L); break;
-        case 6: launch_mega_as<false, 128, 6, false>(L); break;
-        case 7: launch_mega_as<false, 128, 7, false>(L); break;
-        default: launch_mega_as<false, 256, 3, false>(L); break;
+        case 2: launch_mega_as<false, 256, 2, 0>(L); break;
+        case 4: launch_mega_as<false, 256, 4, 0>(L); break;
+        case 5: launch_mega_as<false, 128, 5, 0>(L); break;
+        case 6: launch_mega_as<false, 128, 6, 0>(L); break;
+        case 7: launch_mega_as<false, 128, 7, 0>(L); break;
+        default: launch_mega_as<false, 256, 3, 0>(L); break;
       }
     }
     ++*launches;

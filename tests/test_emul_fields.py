@@ -52,3 +52,17 @@ def test_emul_scatter_materials(rtb, orc, emu):
     fc.check_scatter_material(e, o, w, mats["metal"], "metal", (1.0, -0.05, 0.0), nrm, n=40_000)  # grazing: part absorbed
     for d_in in ((0.3, -1.0, 0.2), (2.0, -0.3, 0.1), (0.2, 1.0, -0.1), (1.0, 0.6, 0.0), (1.0, 0.9, 0.0)):  # outside, grazing, inside, TIR
         fc.check_scatter_material(e, o, w, mats["dielectric"], "dielectric", d_in, nrm, n=40_000)
+
+
+def test_flattener_knows_a_room_from_an_open_scene(rtb, emu):
+    # FlatScene::enclosed picks the point up to which the megakernel scans primitives instead of walking a tree (render.cu)
+    want = {"two_spheres": (2, False), "simple_light": (4, False), "cornell_box": (8, True), "cornell_smoke": (6, True),
+            "random_scene": (None, False), "final_scene": (1407, False)}
+    for name, (prims, enclosed) in want.items():
+        s, w, _ = rtb.Scene.named(name, 16, 16)
+        f = emu.EmuScene(s.serialize(), w).facts()
+        assert f["enclosed"] == enclosed and (prims is None or f["prims"] == prims), (name, f)
+    s = rtb.Scene()  # three walls of a room only: not enclosed
+    m = s.lambertian(s.solid(0.5, 0.5, 0.5))
+    w = s.list([s.rect(0, 0, 0, 10, 10, 0, m), s.rect(1, 0, 0, 10, 10, 0, m), s.rect(2, 0, 0, 10, 10, 10, m)])
+    assert not emu.EmuScene(s.serialize(), w).facts()["enclosed"]

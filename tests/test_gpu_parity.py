@@ -259,8 +259,16 @@ def test_four_wide_tree_traces_the_same_paths_as_the_two_child_tree(rtb, name, b
         assert sa[k] == sb[k], (k, sa[k], sb[k])
     np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-4)
     assert sa["node_tests"] != sb["node_tests"]  # it really was the other tree
+    # ... nor on having a tree at all: the flat scan (every primitive tested where the segment starts) traces the same paths
+    o1 = rtb.default_opts(background=bg, seed=4, collect_stats=1)
+    o1.reserved[6] = 1
+    c, _, sf = s.render(w, cam, nx, ny, ns, o1, want_rgb8=False, want_stats=True)
+    for k in ("paths", "segments", "shade", "tex_evals", "medium_tests"):
+        assert sf[k] == sb[k], (k, sf[k], sb[k])
+    np.testing.assert_allclose(c, b, rtol=1e-4, atol=1e-4)
+    assert sf["node_tests"] == 0 and sf["prim_tests"] >= sb["prim_tests"]
     auto, _, sc = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, collect_stats=1), want_rgb8=False, want_stats=True)
-    assert sc["node_tests"] in (sa["node_tests"], sb["node_tests"]) and sc["segments"] == sa["segments"]
+    assert sc["node_tests"] in (sa["node_tests"], sb["node_tests"], 0) and sc["segments"] == sa["segments"]
     print(name, "node tests (2-box units) per segment: 4-wide", sa["node_tests"] / sa["segments"], "2-wide", sb["node_tests"] / sb["segments"],
           "prim tests per segment", sa["prim_tests"] / sa["segments"], sb["prim_tests"] / sb["segments"])
 

@@ -29,7 +29,7 @@ while time.time() < t_end:
         for i in range(3):
             o.reserved[i] = rnd.choice([0, 1, 4, 8, 16, 32])
         o.reserved[3] = rnd.choice([0, 2, 3, 4, 5, 6, 7])
-        o.reserved[6] = rnd.choice([0, 2, 4])  # tree: upload-time choice / two-child / four-wide
+        o.reserved[6] = rnd.choice([0, 1, 2, 4])  # tree: upload-time choice / flat scan / two-child / four-wide
         if rnd.random() < 0.4:  # a row-band shard on top of the sample shard
             o.band_stride = rnd.choice([2, 3, 8])
             o.band_begin = rnd.randrange(o.band_stride)

@@ -61,6 +61,11 @@ void emu_set_bvh_width(void* p, int width) {
   EmuScene* e = (EmuScene*)p;
   e->view.nodes4 = (width == 4 && !e->flat.nodes4.empty()) ? e->flat.nodes4.data() : nullptr;
 }
+// what the flattener found out about the scene: [0] primitives, [1] FlatScene::enclosed
+void emu_scene_facts(void* p, int* out) {
+  EmuScene* e = (EmuScene*)p;
+  out[0] = (int)e->flat.prims.size(), out[1] = e->flat.enclosed ? 1 : 0;
+}
 void emu_scene_free(void* p) {
   EmuScene* e = (EmuScene*)p;
   if (!e) return;

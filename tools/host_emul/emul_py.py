@@ -24,6 +24,7 @@ _vp, _i, _d, _u64, _sz = C.c_void_p, C.c_int, C.c_double, C.c_uint64, C.c_size_t
 lib.emu_scene_load.restype = _vp
 lib.emu_scene_load.argtypes = [_vp, _sz, _i]
 lib.emu_scene_free.argtypes = [_vp]
+lib.emu_scene_facts.argtypes = [_vp, _vp]
 lib.emu_set_bvh_width.argtypes = [_vp, _i]
 lib.emu_closest_hit_ex.argtypes = [_vp, _vp, _sz, _d, _vp, _vp, _vp, _vp]
 lib.emu_scatter.argtypes = [_vp, _i, _vp, _sz, _u64, _vp]
@@ -48,6 +49,12 @@ class EmuScene:
         p, self._p = getattr(self, "_p", None), None
         if p:
             lib.emu_scene_free(p)
+
+    def facts(self):
+        """{'prims': flattened primitives, 'enclosed': FlatScene::enclosed (>= 4 faces of the world box are walls)}"""
+        out = (C.c_int * 2)()
+        lib.emu_scene_facts(self._p, out)
+        return {"prims": out[0], "enclosed": bool(out[1])}
 
     def set_bvh_width(self, width):
         lib.emu_set_bvh_width(self._p, width)

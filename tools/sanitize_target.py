@@ -17,10 +17,10 @@ for name, nx, ny, ns in (("cornell_smoke_book", 37, 23, 6), ("final_scene_lit", 
         a, r8, st = s.render(w, cam, nx, ny, ns, rtb.default_opts(pipeline=p, background=1), want_stats=True)
         print(name, "pipe", p, "mean", float(a.mean()) / ns, "segments", st["segments"], flush=True)
     o = rtb.default_opts(background=1, collect_stats=1)
-    for width in (2, 4):  # the megakernel on either tree, whatever the upload-time choice was
+    for width in (2, 4, 1):  # the megakernel on either tree and on the flat scan, whatever the upload-time choice was
         o.reserved[6] = width
         a, _, st = s.render(w, cam, nx, ny, ns, o, want_stats=True)
-        print(name, f"mega/bvh{width}", float(a.mean()) / ns, st["segments"], flush=True)
+        print(name, "mega/flat" if width == 1 else f"mega/bvh{width}", float(a.mean()) / ns, st["segments"], flush=True)
     a, _, st = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=1, band_begin=1, band_stride=3, sample_begin=1, sample_stride=2), want_stats=True)
     print(name, "band+sample shard", float(a.mean()) / ns, st["paths"], flush=True)
     rays = rtb.primary_rays(cam, nx, ny)
