@@ -747,7 +747,12 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     P.k_node = o.reserved[0] > 0 ? o.reserved[0] : 4;
     P.k_leaf = o.reserved[1] > 0 ? o.reserved[1] : 4;
     P.k_shade = o.reserved[2] > 0 ? o.reserved[2] : 4;
-    const int min_blocks = o.reserved[3] > 0 ? o.reserved[3] : 3;
+    // which tree: the upload-time choice (ensure_uploaded) unless opts.reserved[6] = 1 / 2 / 4 forces the flat list / the
+    // two-child / the four-wide tree (A/B runs); flat and four-wide have the 256-thread occupancy points only
+    const SceneView view = view_with_width(d, o.reserved[6]);
+    // blocks per SM: 3 x 256 threads at 80 registers (profiles/r2_experiments.txt E14-E17); a flat-scan scene with Perlin
+    // textures runs turbulence on nearly every lane and is 12-14 % faster with 123 registers and no spills (E19)
+    const int min_blocks = o.reserved[3] > 0 ? o.reserved[3] : (view.flat && !d->flat.perlin.empty() ? 2 : 3);
     const long long items = tiles * P.slices;
     if (items > 0x7fffffffLL) return fail(RTB_ERR_INVALID, "render: image too large for one launch");
     P.n_items = (int)items;
@@ -763,9 +768,6 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     const long long blocks = std::min<long long>((items + wpb - 1) / wpb, (long long)d->prop.multiProcessorCount * bps);
     unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
     CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
-    // which tree: the upload-time choice (ensure_uploaded) unless opts.reserved[6] = 1 / 2 / 4 forces the flat list / the
-    // two-child / the four-wide tree (A/B runs); flat and four-wide have the 256-thread occupancy points only
-    const SceneView view = view_with_width(d, o.reserved[6]);
     const bool flat = view.flat != 0 && block == 256, wide = !flat && view.nodes4 != nullptr && block == 256;
     const MegaLaunch L{(unsigned)blocks, stream, &view, &cam, &P, d_sum, d->d_stats, wc, o.reserved[5]};
     if (o.collect_stats) {
