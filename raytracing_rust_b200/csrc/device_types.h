@@ -116,6 +116,17 @@ struct SceneView {
   int flat;  // != 0: the megakernel scans `prims` instead of walking a tree (scenes of a handful of primitives)
 };
 
+// The primitives of a flat-scan scene (k_render_mega kTree = 2) as a kernel parameter: read through the constant bank, grouped
+// by class so that each group's loop tests one known kind of primitive (trace.cuh PrimClass): [0, end[0]) static spheres,
+// [end[0], end[1]) / [end[1], end[2]) / [end[2], end[3]) untransformed YZ / ZX / XY rects, [end[3], n) everything else.
+#define RTB_FLAT_MAX_PRIMS 16
+struct FlatTables {
+  int n;
+  int end[4];
+  int index[RTB_FLAT_MAX_PRIMS];  // position of each record in SceneView::prims (what Hit::prim / self_prim name)
+  DPrim prims[RTB_FLAT_MAX_PRIMS];
+};
+
 struct DCamera {  // src/camera.rs:8-18, f32
   float origin[3], llc[3], horizontal[3], vertical[3], u[3], v[3];
   float time0, time1, lens_radius;

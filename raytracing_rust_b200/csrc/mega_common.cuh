@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "device_types.h"
 #include "philox.h"
 
 namespace rtb {

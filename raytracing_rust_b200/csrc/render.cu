@@ -101,7 +101,8 @@ __device__ __forceinline__ int tid_here() {
 template <bool kStats, int kThreads, int kMinBlocks, int kTree>
 __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView sv, DCamera cam, MegaParams P, float* __restrict__ accum,
                                                         unsigned long long* __restrict__ stats,
-                                                        unsigned int* __restrict__ work_counter) {
+                                                        unsigned int* __restrict__ work_counter,
+                                                        const __grid_constant__ FlatTables FT) {
   // Two accumulation tiles per warp: generation g of the warp's item sequence adds into s_acc[.][g & 1],
   // so paths of the previous item may still be in flight while the next item's paths start.
   constexpr bool kWide = kTree == 1, kFlat = kTree == 2;
@@ -324,16 +325,29 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks) k_render_mega(SceneView 
           ri = make_ray_inv(ray);
           inv_a = rcp_fast(dot(ray.d, ray.d));
           best.t = CUDART_INF_F, best.prim = -1, best.face = 0, best.id = -1;
-          if (kFlat) {  // the whole closest-hit query here: every primitive, same acceptance and tie rule as the LEAF phase
-            for (int pi = 0; pi < sv.n_prims; ++pi) {
-              float t;
-              int face, id;
-              if (intersect_prim<kStats>(sv.prims, pi, sv.xforms, ray, inv_a, P.t_min, best.t, pi == self_prim, self_face, &t,
-                                         &face, &id, &cnt) &&
-                  (t < best.t || id > best.id)) {
-                best.t = t, best.prim = pi, best.face = face, best.id = id;
-              }
-            }
+          if (kFlat) {  // the whole closest-hit query here: every primitive, same acceptance and tie rule as the LEAF phase,
+            // class by class (FlatTables) so each loop body is one specialised test on constant-bank operands
+#define RTB_FLAT_LOOP(CLASS, END)                                                                                        \
+  for (; fi < (END); ++fi) {                                                                                             \
+    const int pi = FT.index[fi];                                                                                         \
+    const float4 A = make_float4(FT.prims[fi].a.x, FT.prims[fi].a.y, FT.prims[fi].a.z, FT.prims[fi].a.w);                \
+    const float4 B = make_float4(FT.prims[fi].b.x, FT.prims[fi].b.y, FT.prims[fi].b.z, FT.prims[fi].b.w);                \
+    const int4 C = make_int4(FT.prims[fi].c.x, FT.prims[fi].c.y, FT.prims[fi].c.z, FT.prims[fi].c.w);                    \
+    float t;                                                                                                             \
+    int face, id;                                                                                                        \
+    if (intersect_prim_abc<kStats, CLASS>(A, B, C, sv.xforms, ray, inv_a, P.t_min, best.t, pi == self_prim, self_face,   \
+                                          &t, &face, &id, &cnt) &&                                                       \
+        (t < best.t || id > best.id)) {                                                                                  \
+      best.t = t, best.prim = pi, best.face = face, best.id = id;                                                        \
+    }                                                                                                                    \
+  }
+            int fi = 0;
+            RTB_FLAT_LOOP(PC_SPHERE, FT.end[0])
+            RTB_FLAT_LOOP(PC_RECT_YZ, FT.end[1])
+            RTB_FLAT_LOOP(PC_RECT_ZX, FT.end[2])
+            RTB_FLAT_LOOP(PC_RECT_XY, FT.end[3])
+            RTB_FLAT_LOOP(PC_ANY, FT.n)
+#undef RTB_FLAT_LOOP
             cur = CUR_SHADE;
           } else {
             top = stack + 1;
@@ -473,7 +487,7 @@ SceneView view_with_width(const DeviceScene* d, int width) {
   SceneView v = d->view;
   if (width == 0)
     if (const char* e = std::getenv("RTB200_BVH_WIDTH")) width = std::atoi(e);
-  if (width == 1) v.flat = 1;  // (a scene of any size: experiments and the same-paths test)
+  if (width == 1) v.flat = d->flat_tables.n == (int)d->flat.prims.size() ? 1 : 0;  // (only scenes that fit FlatTables)
   else if (width == 2) v.nodes4 = nullptr, v.flat = 0;
   else if (width == 4 && d->d_nodes4) v.nodes4 = d->d_nodes4, v.flat = 0;
   return v;
@@ -614,7 +628,22 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   {  // scenes of a handful of primitives are scanned, not traversed (k_render_mega kTree = 2); RTB200_FLAT_MAX overrides
     static const int flat_max = std::getenv("RTB200_FLAT_MAX") ? std::atoi(std::getenv("RTB200_FLAT_MAX")) : -1;
     const int limit = flat_max >= 0 ? flat_max : (f.enclosed ? kFlatMaxPrimsEnclosed : kFlatMaxPrimsOpen);
-    v.flat = (int)f.prims.size() <= limit ? 1 : 0;
+    v.flat = (int)f.prims.size() <= limit && f.prims.size() <= RTB_FLAT_MAX_PRIMS ? 1 : 0;
+    FlatTables& ft = d->flat_tables;
+    ft = FlatTables{};
+    if (f.prims.size() <= RTB_FLAT_MAX_PRIMS) {  // grouped by class (mega_common.cuh); the order inside a group does not matter
+      auto cls = [](const DPrim& p) {
+        const int type = RTB_PRIM_TYPE(p.c.x);
+        if (type == DP_SPHERE) return 0;
+        if (type == DP_RECT && RTB_PRIM_XFORM(p.c.x) == 0) return 1 + RTB_PRIM_PLANE(p.c.x);
+        return 4;
+      };
+      for (int c = 0; c <= 4; ++c) {
+        for (size_t i = 0; i < f.prims.size(); ++i)
+          if (cls(f.prims[i]) == c) ft.index[ft.n] = (int)i, ft.prims[ft.n] = f.prims[i], ++ft.n;
+        if (c < 4) ft.end[c] = ft.n;
+      }
+    }
   }
   void* st = nullptr;
   CUDA_TRY(pool_alloc(device, 32 * sizeof(unsigned long long), &st));
@@ -677,6 +706,7 @@ struct MegaLaunch {
   unsigned long long* d_stats;
   unsigned int* work_counter;
   int carveout_override;  // opts.reserved[5] (experiments)
+  const FlatTables* flat;  // the scene's primitives by class (flat scan), or an empty table
 };
 
 // One instantiation of the megakernel.  Shared-memory carveout: just what the resident blocks need (the kernel's static
@@ -691,7 +721,7 @@ static void launch_mega_as(const MegaLaunch& L) {
   }();
   cudaFuncSetAttribute(k_render_mega<ST, TH, MB, WD>, cudaFuncAttributePreferredSharedMemoryCarveout,
                        L.carveout_override > 0 ? L.carveout_override : carveout);
-  k_render_mega<ST, TH, MB, WD><<<L.blocks, TH, 0, L.stream>>>(*L.view, *L.cam, *L.P, L.d_sum, L.d_stats, L.work_counter);
+  k_render_mega<ST, TH, MB, WD><<<L.blocks, TH, 0, L.stream>>>(*L.view, *L.cam, *L.P, L.d_sum, L.d_stats, L.work_counter, *L.flat);
 }
 
 static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int ns, const rtb_render_opts& o, float* d_sum,
@@ -769,7 +799,7 @@ static int launch_mega(DeviceScene* d, const DCamera& cam, int nx, int ny, int n
     unsigned int* wc = d->d_work;  // launches of one scene are serialised on `stream`
     CUDA_TRY(cudaMemsetAsync(wc, 0, sizeof(unsigned int), stream));
     const bool flat = view.flat != 0 && block == 256, wide = !flat && view.nodes4 != nullptr && block == 256;
-    const MegaLaunch L{(unsigned)blocks, stream, &view, &cam, &P, d_sum, d->d_stats, wc, o.reserved[5]};
+    const MegaLaunch L{(unsigned)blocks, stream, &view, &cam, &P, d_sum, d->d_stats, wc, o.reserved[5], &d->flat_tables};
     if (o.collect_stats) {
       if (block != 256) launch_mega_as<true, 128, 4, 0>(L);
       else if (flat) launch_mega_as<true, 256, 2, 2>(L);

@@ -25,6 +25,7 @@ struct DeviceScene {
   cudaDeviceProp prop{};
   WavefrontState* wf = nullptr;
   int n_nodes_device = 0;  // BVH nodes resident on the device (host- or device-built)
+  FlatTables flat_tables{};  // the primitives by class when the scene fits the flat scan (<= RTB_FLAT_MAX_PRIMS), else n = 0
   const DNode4* d_nodes4 = nullptr;  // the four-wide form of the tree (host builder only); view.nodes4 = this or nullptr
 };
 

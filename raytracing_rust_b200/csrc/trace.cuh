@@ -213,19 +213,20 @@ struct Counters {
 //           {slab entry, slab exit} inside [t_min, t_max].
 // Plane distances are always (k - o) * rcp(d), in Rect and Box alike, so coincident planes
 // (a cube standing on a floor rect) produce bit-identical t and the ID tie rule can apply.
-template <bool kStats>
-RTB_DEV bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXform* __restrict__ xforms,
-                                               const RayF& ray, float inv_a, float t_min, float t_max, bool self,
-                                               int self_face, float* t_out, int* face_out, int* id_out, Counters* cnt) {
+// kClass: what the caller knows about the record at compile time (the flat scan of render.cu walks its primitives class by
+// class, so the type / plane / transform tests and the axis selects fold away; the arithmetic is the same either way).
+enum PrimClass { PC_ANY = -1, PC_SPHERE = 0, PC_RECT_YZ = 1, PC_RECT_ZX = 2, PC_RECT_XY = 3 };  // rect classes: no transform
+template <bool kStats, int kClass>
+RTB_DEV bool intersect_prim_abc(const float4 A, const float4 B, const int4 C, const DXform* __restrict__ xforms,
+                                const RayF& ray, float inv_a, float t_min, float t_max, bool self,
+                                int self_face, float* t_out, int* face_out, int* id_out, Counters* cnt) {
   if (kStats) cnt->prim_tests++;
-  const float4 A = ldg4(&prims[pi].a);
-  const float4 B = ldg4(&prims[pi].b);
-  const int4 C = ldg4i(&prims[pi].c);
-  const int type = RTB_PRIM_TYPE(C.x);
+  const bool k_rect = kClass >= PC_RECT_YZ && kClass <= PC_RECT_XY;
+  const int type = kClass == PC_SPHERE ? (int)DP_SPHERE : (k_rect ? (int)DP_RECT : RTB_PRIM_TYPE(C.x));
   *id_out = C.z;
   *face_out = 0;
   if (type <= DP_MOVING_SPHERE) {
-    V3f ctr = sphere_center(A, B, C, ray.time);
+    V3f ctr = kClass == PC_SPHERE ? mk(A.x, A.y, A.z) : sphere_center(A, B, C, ray.time);
     V3f oc = ray.o - ctr;
     float b = dot(oc, ray.d);
     float tc = -b * inv_a;
@@ -248,7 +249,7 @@ RTB_DEV bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXfor
   }
   // planar primitives live in the local space of their instance transform
   V3f o = ray.o, d = ray.d;
-  const int xi = RTB_PRIM_XFORM(C.x);
+  const int xi = k_rect ? 0 : RTB_PRIM_XFORM(C.x);
   if (xi != 0) {
     DXform x = load_xform(xforms, xi);
     o = xf_point(x, ray.o);
@@ -256,7 +257,7 @@ RTB_DEV bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXfor
   }
   if (type == DP_RECT) {
     if (self) return false;  // a ray leaving a plane never meets it again
-    const int plane = RTB_PRIM_PLANE(C.x);
+    const int plane = k_rect ? kClass - PC_RECT_YZ : RTB_PRIM_PLANE(C.x);
     const int k_axis = plane, a_axis = plane == 2 ? 0 : plane + 1, b_axis = plane == 0 ? 2 : plane - 1;
     float t = (B.x - comp(o, k_axis)) * rcp_fast(comp(d, k_axis));
     if (t < t_min || t > t_max) return false;
@@ -308,6 +309,17 @@ RTB_DEV bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXfor
   *face_out = face;
   *id_out = C.z + face;
   return true;
+}
+
+// the record fetched from the primitive table (3 x LDG.128)
+template <bool kStats>
+RTB_DEV bool intersect_prim(const DPrim* __restrict__ prims, int pi, const DXform* __restrict__ xforms,
+                                               const RayF& ray, float inv_a, float t_min, float t_max, bool self,
+                                               int self_face, float* t_out, int* face_out, int* id_out, Counters* cnt) {
+  const float4 A = ldg4(&prims[pi].a);
+  const float4 B = ldg4(&prims[pi].b);
+  const int4 C = ldg4i(&prims[pi].c);
+  return intersect_prim_abc<kStats, PC_ANY>(A, B, C, xforms, ray, inv_a, t_min, t_max, self, self_face, t_out, face_out, id_out, cnt);
 }
 
 // ---- BVH node step -----------------------------------------------------------------------------

@@ -266,7 +266,10 @@ def test_four_wide_tree_traces_the_same_paths_as_the_two_child_tree(rtb, name, b
     for k in ("paths", "segments", "shade", "tex_evals", "medium_tests"):
         assert sf[k] == sb[k], (k, sf[k], sb[k])
     np.testing.assert_allclose(c, b, rtol=1e-4, atol=1e-4)
-    assert sf["node_tests"] == 0 and sf["prim_tests"] >= sb["prim_tests"]
+    if name in ("cornell_box", "cornell_smoke_book", "earth", "two_spheres"):  # scenes that fit the flat scan's table (<= 16 primitives)
+        assert sf["node_tests"] == 0 and sf["prim_tests"] >= sb["prim_tests"]
+    else:                                                                       # larger ones keep their tree when asked for it
+        assert sf["node_tests"] in (sa["node_tests"], sb["node_tests"])
     auto, _, sc = s.render(w, cam, nx, ny, ns, rtb.default_opts(background=bg, seed=4, collect_stats=1), want_rgb8=False, want_stats=True)
     assert sc["node_tests"] in (sa["node_tests"], sb["node_tests"], 0) and sc["segments"] == sa["segments"]
     print(name, "node tests (2-box units) per segment: 4-wide", sa["node_tests"] / sa["segments"], "2-wide", sb["node_tests"] / sb["segments"],
