@@ -628,10 +628,12 @@ int ensure_uploaded(rtb_scene* s, int world, int device, double tlo, double thi)
   {  // scenes of a handful of primitives are scanned, not traversed (k_render_mega kTree = 2); RTB200_FLAT_MAX overrides
     static const int flat_max = std::getenv("RTB200_FLAT_MAX") ? std::atoi(std::getenv("RTB200_FLAT_MAX")) : -1;
     const int limit = flat_max >= 0 ? flat_max : (f.enclosed ? kFlatMaxPrimsEnclosed : kFlatMaxPrimsOpen);
-    v.flat = (int)f.prims.size() <= limit && f.prims.size() <= RTB_FLAT_MAX_PRIMS ? 1 : 0;
+    // (the device builder reorders the primitives on the device: a forced LBVH keeps its tree)
+    const bool fits = !device_bvh && f.prims.size() <= RTB_FLAT_MAX_PRIMS;
+    v.flat = fits && (int)f.prims.size() <= limit ? 1 : 0;
     FlatTables& ft = d->flat_tables;
     ft = FlatTables{};
-    if (f.prims.size() <= RTB_FLAT_MAX_PRIMS) {  // grouped by class (mega_common.cuh); the order inside a group does not matter
+    if (fits) {  // grouped by class (mega_common.cuh); the order inside a group does not matter
       auto cls = [](const DPrim& p) {
         const int type = RTB_PRIM_TYPE(p.c.x);
         if (type == DP_SPHERE) return 0;

@@ -1,5 +1,5 @@
 #!/bin/bash
-# r2 GPU call 7: the flat scan (E19) as the default on small scenes: whole -m gpu suite, self-check build, tree A/B with the automatic choice, configs
+# r2 GPU call 7: the flat scan (E19, E20) as the default on small scenes: whole -m gpu suite, self-check build, tree A/B with the automatic choice, configs
 cd "$(dirname "$0")/.."
 O=gpurun_out
 python -m pytest tests -m gpu -q -rP > $O/r2_gputest7.log 2>&1; echo "pytest rc=$?"; tail -3 $O/r2_gputest7.log
