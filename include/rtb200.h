@@ -145,7 +145,10 @@ typedef struct rtb_render_opts {
   int band_begin;      /* row-band sharding (the "image tiles" split of the pixel loop, tests/test.rs:62-63): this call */
   int band_stride;     /* renders the 4-row bands b = band_begin + i*band_stride of the image; 0,1 (or 0,0) for all rows */
   int multi_shard;     /* rtb_render_multi only: RtbMultiShard — how the call splits the work over its devices */
-  int reserved[7];
+  int reserved[7];     /* 0 = defaults.  Tuning / experiment knobs of the megakernel, no effect on the result beyond float
+                        * summation order: [0..2] lanes a NODE / LEAF / SHADE round waits for, [3] occupancy point (2..4 blocks
+                        * of 256 threads per SM, 5..7 of 128), [4] wavefront pipeline: path slots, [5] shared-memory carveout %,
+                        * [6] closest-hit form: 1 flat scan (scenes of <= 16 primitives), 2 two-child BVH, 4 four-wide BVH */
 } rtb_render_opts;
 /* rtb_render_multi: RTB_SHARD_SAMPLES — device g renders samples g, g+G, ... of every pixel, one sum-reduce closes the
  * image (best when there are many samples per pixel); RTB_SHARD_BANDS — device g renders every sample of the 4-row bands
