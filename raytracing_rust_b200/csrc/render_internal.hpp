@@ -29,8 +29,9 @@ struct DeviceScene {
   const DNode4* d_nodes4 = nullptr;  // the four-wide form of the tree (host builder only); view.nodes4 = this or nullptr
 };
 
-// The scene tables as a kernel should see them: width 0 = the upload-time choice of tree (d->view), 2 = the two-child
-// tree, 4 = the four-wide tree when it exists.  RTB200_BVH_WIDTH=2|4 in the environment overrides width 0 (experiments).
+// The scene tables as a kernel should see them: width 0 = the upload-time choice (d->view), 1 = no tree (the megakernel's flat
+// scan; only scenes that fit FlatTables), 2 = the two-child tree, 4 = the four-wide tree when it exists.  RTB200_BVH_WIDTH=1|2|4
+// in the environment overrides width 0 (experiments).
 SceneView view_with_width(const DeviceScene* d, int width);
 
 // bvh_build.cu: LBVH over d->flat.prims on the device; sets view.nodes / view.prims / flat.root / flat.bvh_depth
