@@ -23,3 +23,22 @@ def rtb():
 def orc():
     from oracle import oracle_py as m
     return m
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """Under the self-checking build (RTB200_LIB = a -DRTB_DEBUG_CHECKS=1 library, profiles/r2_sanitizer.txt) every kernel
+    bounds-checks the indices it forms; after a -m gpu run report the device counters and fail the session if any is set."""
+    import os
+    if "checks" not in os.environ.get("RTB200_LIB", ""):
+        return
+    try:
+        import raytracing_rust_b200 as m
+        if m.device_count() == 0:
+            return
+        c = m.check_failures()
+    except Exception as e:  # a release build answers with an error: nothing to report
+        print(f"\n[rtb200 self-checks] not available: {e}")
+        return
+    print(f"\n[rtb200 self-checks] device counters after the session: {c}")
+    if any(c.values()):
+        session.exitstatus = 1
